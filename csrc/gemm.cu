@@ -1,0 +1,468 @@
+// bf16 GEMM on 5th-gen tensor cores: C[M,N] (+)= A[M,K] * B[N,K]^T, fp32 accumulation in TMEM.
+//
+// Persistent, warp-specialised, one CTA per SM:
+//   warp 0      TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx)
+//   warp 1      MMA issuer    (one elected lane: tcgen05.mma 128x256x16, tcgen05.commit)
+//   warps 2..5  epilogue      (tcgen05.ld from TMEM -> convert -> global), overlapped with the next
+//                              tile's MMAs through two 256-column TMEM accumulators.
+// Operand layouts: K-major or MN-major for either operand (forward / dgrad / wgrad of a Linear run
+// on the same kernel without materialised transposes).  The epilogue can instead reduce each tile to
+// log-softmax partials (fused lm_head log-prob).
+//
+// Reference path replaced: nn.Linear -> cuBLASLt (R/src/training/train_dpo.py:32) and
+// log_softmax + gather over the vocab (R/src/training/train_dpo.py:33-38).
+#include <math.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "tc_common.cuh"
+
+namespace dla {
+
+// ------------------------------------------------------------------ host: tensor-map encode
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  });
+  return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, uint64_t ld_elems,
+                      uint32_t box0, uint32_t box1) {
+  PFN_encodeTiled fn = get_encode_fn();
+  DLA_REQUIRE(fn != nullptr, DLA_E_DRIVER, "cuTensorMapEncodeTiled entry point not available");
+  DLA_REQUIRE(((uintptr_t)base & 15) == 0 && (ld_elems * 2) % 16 == 0, DLA_E_BADARG,
+              "tensor map: base must be 16-byte aligned and the row pitch a multiple of 8 elements (ld=%llu)",
+              (unsigned long long)ld_elems);
+  cuuint64_t dims[2] = {dim0, dim1};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DLA_REQUIRE(r == CUDA_SUCCESS, DLA_E_DRIVER, "cuTensorMapEncodeTiled failed with %d (dims %llu x %llu, ld %llu, box %u x %u)",
+              (int)r, (unsigned long long)dim0, (unsigned long long)dim1, (unsigned long long)ld_elems, box0, box1);
+  return 0;
+}
+
+// ------------------------------------------------------------------ kernel
+namespace gemm {
+
+constexpr int BM = 128;          // rows of A per CTA tile (= TMEM lanes)
+constexpr int BN = 256;          // columns per tile (= UMMA N, one TMEM accumulator)
+constexpr int BK = 64;           // 64 bf16 = 128 B = one swizzle span
+constexpr int UMMA_K = 16;
+constexpr int kStages = 4;
+constexpr int A_BYTES = BM * BK * 2;   // 16 KiB
+constexpr int B_BYTES = BN * BK * 2;   // 32 KiB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int kThreads = 192;
+constexpr int kEpiWarps = 4;
+constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int GROUP_M = 16;
+
+enum Epi { kStore = 0, kLogprob = 1 };
+
+struct Params {
+  int M, N, K;
+  void* C;
+  int64_t ldc;
+  int c_fp32, accumulate;
+  int num_m_tiles, num_n_tiles;
+  // log-prob epilogue
+  const int64_t* labels;
+  float2* partials;   // [num_n_tiles, M] (max, sumexp)
+  float* picked;      // [M] logit at the label
+};
+
+__device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int& m_blk, int& n_blk) {
+  const int per_group = GROUP_M * num_n;
+  const int g = t / per_group;
+  const int first_m = g * GROUP_M;
+  const int gsz = min(num_m - first_m, GROUP_M);
+  const int r = t - g * per_group;
+  m_blk = first_m + r % gsz;
+  n_blk = r / gsz;
+}
+
+template <bool kAMN, bool kBMN, int kEpi>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_kb = (p.K + BK - 1) / BK;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tc::prefetch_tmap(&tmA);
+    tc::prefetch_tmap(&tmB);
+    for (int s = 0; s < kStages; ++s) {
+      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      tc::mbar_init(&tfull_bar[a], 1);
+      tc::mbar_init(&tempty_bar[a], kEpiWarps);
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) tc::tmem_alloc<1>(tmem_holder, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        int m_blk, n_blk;
+        tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+        const int m0 = m_blk * BM, n0 = n_blk * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          tc::mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          const int k0 = kb * BK;
+          if constexpr (!kAMN) {
+            tc::tma_load_2d(sa, &tmA, &full_bar[stage], k0, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c) tc::tma_load_2d(sa + c * (64 * BK * 2), &tmA, &full_bar[stage], m0 + c * 64, k0);
+          }
+          if constexpr (!kBMN) {
+            tc::tma_load_2d(sb, &tmB, &full_bar[stage], k0, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BN / 64; ++c) tc::tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[stage], n0 + c * 64, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, kAMN ? 1 : 0, kBMN ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(&full_bar[stage], phase);
+          tc::tc_fence_after();
+          const uint32_t sa = tc::smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // K-major: step 16 elements = 32 B inside the 128 B swizzle span.
+            // MN-major: step 16 K-rows of 128 B = 2048 B; LBO = 8 KiB between 64-wide MN chunks.
+            const uint64_t da = kAMN ? tc::make_smem_desc(sa + k * 2048, 64 * BK * 2, 1024)
+                                     : tc::make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t db = kBMN ? tc::make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024)
+                                     : tc::make_smem_desc(sb + k * 32, 16, 1024);
+            tc::umma_bf16<1>(tmem_d, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          tc::umma_commit(&empty_bar[stage]);       // smem slot reusable once these MMAs retire
+          if (kb == num_kb - 1) tc::umma_commit(&tfull_bar[acc]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+    int it = 0;
+    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      int m_blk, n_blk;
+      tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      tc::mbar_wait(&tfull_bar[acc], acc_phase);
+      tc::tc_fence_after();
+      const int row = m_blk * BM + quarter * 32 + lane;
+      const int col_base = n_blk * BN;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
+
+      if constexpr (kEpi == kStore) {
+#pragma unroll 1
+        for (int ch = 0; ch < BN / 32; ++ch) {
+          uint32_t r[32];
+          tc::tmem_ld_32x32(taddr + ch * 32, r);
+          tc::tmem_ld_wait();
+          const int col0 = col_base + ch * 32;
+          if (row < p.M && col0 < p.N) {
+            const bool full = (col0 + 32 <= p.N);
+            if (p.c_fp32) {
+              float* dst = reinterpret_cast<float*>(p.C) + (int64_t)row * p.ldc + col0;
+              if (full && (p.ldc & 3) == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                  float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+                  if (p.accumulate) {
+                    const float4 o = *reinterpret_cast<const float4*>(dst + j);
+                    v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+                  }
+                  *reinterpret_cast<float4*>(dst + j) = v;
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (col0 + j < p.N) dst[j] = __uint_as_float(r[j]) + (p.accumulate ? dst[j] : 0.f);
+              }
+            } else {
+              bf16* dst = reinterpret_cast<bf16*>(p.C) + (int64_t)row * p.ldc + col0;
+              if (full && (p.ldc & 7) == 0) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                  float f[8];
+#pragma unroll
+                  for (int q = 0; q < 8; ++q) f[q] = __uint_as_float(r[j + q]);
+                  if (p.accumulate) {
+                    float o[8];
+                    unpack8(ld8(dst + j), o);
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) f[q] += o[q];
+                  }
+                  st8(dst + j, pack8(f));
+                }
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (col0 + j < p.N)
+                    dst[j] = __float2bfloat16(__uint_as_float(r[j]) + (p.accumulate ? __bfloat162float(dst[j]) : 0.f));
+              }
+            }
+          }
+        }
+      } else {
+        // ---- fused log-softmax partials: (max, sum exp(x - max)) of this row over the tile's columns
+        constexpr float kLog2e = 1.4426950408889634f;
+        float mx = -INFINITY, sum = 0.f, picked = 0.f;
+        bool has_pick = false;
+        int rel = -1;
+        if (row < p.M) {
+          const int64_t lab = p.labels[row];
+          if (lab >= col_base && lab < col_base + BN) rel = (int)(lab - col_base);
+        }
+#pragma unroll 1
+        for (int ch = 0; ch < BN / 32; ++ch) {
+          uint32_t r[32];
+          tc::tmem_ld_32x32(taddr + ch * 32, r);
+          tc::tmem_ld_wait();
+          const int col0 = col_base + ch * 32;
+          if (col0 >= p.N) continue;
+          const int nvalid = min(32, p.N - col0);
+          float cm = -INFINITY;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < nvalid) cm = fmaxf(cm, __uint_as_float(r[j]));
+          const float nm = fmaxf(mx, cm);
+          float cs = 0.f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j < nvalid) cs += exp2f((__uint_as_float(r[j]) - nm) * kLog2e);
+          sum = sum * exp2f((mx - nm) * kLog2e) + cs;
+          mx = nm;
+          if ((rel >> 5) == ch && rel >= 0) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j == (rel & 31)) picked = __uint_as_float(r[j]);
+            has_pick = true;
+          }
+        }
+        if (row < p.M) {
+          p.partials[(int64_t)n_blk * p.M + row] = make_float2(mx, sum);
+          if (has_pick) p.picked[row] = picked;
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty_bar[acc]);
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+// Combine per-tile (max, sumexp) partials into lse and the label log-prob.
+__global__ void logprob_combine_kernel(const float2* __restrict__ partials, const float* __restrict__ picked,
+                                       const int64_t* __restrict__ labels, int M, int num_n_tiles,
+                                       float* __restrict__ logp, float* __restrict__ lse) {
+  const int m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= M) return;
+  float mx = -INFINITY, sum = 0.f;
+  for (int t = 0; t < num_n_tiles; ++t) {
+    const float2 v = partials[(int64_t)t * M + m];
+    const float nm = fmaxf(mx, v.x);
+    sum = sum * __expf(mx - nm) + v.y * __expf(v.x - nm);
+    mx = nm;
+  }
+  const float l = mx + logf(sum);
+  if (lse != nullptr) lse[m] = l;
+  logp[m] = labels[m] >= 0 ? picked[m] - l : 0.f;
+}
+
+// In place on a bf16 logits chunk: g * (onehot - softmax)
+__global__ void __launch_bounds__(256)
+logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, const int64_t* __restrict__ labels,
+                    const float* __restrict__ grow, int Mc, int V, int64_t ld) {
+  const int m = blockIdx.y;
+  if (m >= Mc) return;
+  const float g = grow[m];
+  const float l = lse[m];
+  const int64_t lab = labels[m];
+  bf16* row = logits + (int64_t)m * ld;
+  const int nvec = V >> 3;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(ld8(row + i * 8), f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float pr = __expf(f[j] - l);
+      f[j] = g * (((int64_t)(i * 8 + j) == lab ? 1.f : 0.f) - pr);
+    }
+    st8(row + i * 8, pack8(f));
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (V & 7)) {
+    const int c = (nvec << 3) + threadIdx.x;
+    const float pr = __expf(__bfloat162float(row[c]) - l);
+    row[c] = __float2bfloat16(g * ((c == lab ? 1.f : 0.f) - pr));
+  }
+}
+
+static int g_variant = 0;
+
+template <bool kAMN, bool kBMN, int kEpi>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, cudaStream_t stream) {
+  auto kern = gemm_kernel<kAMN, kBMN, kEpi>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr_set = true;
+  }
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
+  kern<<<grid, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, p);
+  return check_launch("gemm_bf16");
+}
+
+static int build_maps(CUtensorMap* tmA, CUtensorMap* tmB, const void* A, const void* B, int M, int N, int K,
+                      int64_t lda, int64_t ldb, int a_mn, int b_mn) {
+  int rc;
+  if (!a_mn) rc = make_tmap_2d_bf16(tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
+  else       rc = make_tmap_2d_bf16(tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn) rc = make_tmap_2d_bf16(tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, BN);
+  else       rc = make_tmap_2d_bf16(tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
+  return rc;
+}
+
+}  // namespace gemm
+}  // namespace dla
+
+using namespace dla;
+using namespace dla::gemm;
+
+extern "C" {
+
+int dla_gemm_set_variant(int variant) {
+  g_variant = variant;
+  return 0;
+}
+
+int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                  int a_mn_major, int b_mn_major, int c_fp32, int accumulate, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M > 0 && N > 0 && K > 0, DLA_E_BADARG, "gemm: empty problem %dx%dx%d", M, N, K);
+  DLA_REQUIRE(K % 8 == 0, DLA_E_BADARG, "gemm: K=%d must be a multiple of 8", K);
+  DLA_REQUIRE(!a_mn_major || M % 8 == 0, DLA_E_BADARG, "gemm: MN-major A needs M %% 8 == 0 (M=%d)", M);
+  DLA_REQUIRE(!b_mn_major || N % 8 == 0, DLA_E_BADARG, "gemm: MN-major B needs N %% 8 == 0 (N=%d)", N);
+  CUtensorMap tmA, tmB;
+  int rc = build_maps(&tmA, &tmB, A, B, M, N, K, lda, ldb, a_mn_major, b_mn_major);
+  if (rc) return rc;
+  Params p{};
+  p.M = M; p.N = N; p.K = K; p.C = C; p.ldc = ldc; p.c_fp32 = c_fp32; p.accumulate = accumulate;
+  p.num_m_tiles = (M + BM - 1) / BM;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!a_mn_major && !b_mn_major) return launch<false, false, kStore>(tmA, tmB, p, s);
+  if (!a_mn_major && b_mn_major) return launch<false, true, kStore>(tmA, tmB, p, s);
+  if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, p, s);
+  return launch<true, true, kStore>(tmA, tmB, p, s);
+}
+
+size_t dla_lmhead_scratch_bytes(int M, int V) {
+  const size_t nt = (size_t)(V + BN - 1) / BN;
+  return nt * (size_t)M * sizeof(float2) + (size_t)M * sizeof(float) + 256;
+}
+
+int dla_lmhead_logprob(const void* X, const void* W, const int64_t* labels, int M, int V, int K, int64_t ldx,
+                       int64_t ldw, void* scratch, float* logp, float* lse, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M > 0 && V > 0 && K > 0 && K % 8 == 0, DLA_E_BADARG, "lmhead_logprob: bad shape M=%d V=%d K=%d", M, V, K);
+  DLA_REQUIRE(scratch != nullptr && logp != nullptr, DLA_E_BADARG, "lmhead_logprob: scratch and logp are required");
+  CUtensorMap tmA, tmB;
+  int rc = build_maps(&tmA, &tmB, X, W, M, V, K, ldx, ldw, 0, 0);
+  if (rc) return rc;
+  Params p{};
+  p.M = M; p.N = V; p.K = K;
+  p.num_m_tiles = (M + BM - 1) / BM;
+  p.num_n_tiles = (V + BN - 1) / BN;
+  p.labels = labels;
+  p.partials = reinterpret_cast<float2*>(scratch);
+  p.picked = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + (size_t)p.num_n_tiles * M * sizeof(float2));
+  cudaStream_t s = (cudaStream_t)stream;
+  rc = launch<false, false, kLogprob>(tmA, tmB, p, s);
+  if (rc) return rc;
+  logprob_combine_kernel<<<(M + 255) / 256, 256, 0, s>>>(p.partials, p.picked, labels, M, p.num_n_tiles, logp, lse);
+  return check_launch("lmhead_logprob.combine");
+}
+
+int dla_logprob_grad_inplace(void* logits, const float* lse, const int64_t* labels, const float* grow, int Mc, int V,
+                             int64_t ld, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(ld % 8 == 0, DLA_E_BADARG, "logprob_grad: ld=%lld must be a multiple of 8", (long long)ld);
+  if (Mc == 0) return 0;
+  int bx = ((V >> 3) + 255) / 256;
+  if (bx > 64) bx = 64;
+  if (bx < 1) bx = 1;
+  dim3 grid(bx, Mc);
+  logprob_grad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((bf16*)logits, lse, labels, grow, Mc, V, ld);
+  return check_launch("logprob_grad");
+}
+
+}  // extern "C"

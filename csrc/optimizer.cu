@@ -1,0 +1,190 @@
+// Fused AdamW over flat shards, global grad-norm pieces, dtype casts.
+// Replaces torch.optim.AdamW foreach kernels + clip_grad_norm_.
+#include "common.cuh"
+
+namespace dla {
+
+constexpr int kSumsqBlocks = kNumSMs * 8;
+constexpr int kSumsqThreads = 256;
+
+// One thread = 8 consecutive elements: 16 B of grad, 3 x 32 B of fp32 state in, 3 x 32 B + 16 B out.
+template <bool kGradF32>
+__global__ void __launch_bounds__(256)
+adamw_kernel(float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+             const void* __restrict__ grad, bf16* __restrict__ param, int64_t n, float lr, float beta1,
+             float beta2, float eps, float wd, float inv_bc1, float inv_sqrt_bc2,
+             const float* __restrict__ grad_scale_dev, float prescale) {
+  const float gs = prescale * (grad_scale_dev != nullptr ? *grad_scale_dev : 1.f);
+  const int64_t nvec = n >> 3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = i * 8;
+    float g[8], p[8], mm[8], vv[8];
+    if (kGradF32) {
+      *reinterpret_cast<float4*>(g) = *reinterpret_cast<const float4*>((const float*)grad + o);
+      *reinterpret_cast<float4*>(g + 4) = *reinterpret_cast<const float4*>((const float*)grad + o + 4);
+    } else {
+      unpack8(ld8_stream((const bf16*)grad + o), g);
+    }
+    *reinterpret_cast<float4*>(p) = *reinterpret_cast<const float4*>(master + o);
+    *reinterpret_cast<float4*>(p + 4) = *reinterpret_cast<const float4*>(master + o + 4);
+    *reinterpret_cast<float4*>(mm) = *reinterpret_cast<const float4*>(m + o);
+    *reinterpret_cast<float4*>(mm + 4) = *reinterpret_cast<const float4*>(m + o + 4);
+    *reinterpret_cast<float4*>(vv) = *reinterpret_cast<const float4*>(v + o);
+    *reinterpret_cast<float4*>(vv + 4) = *reinterpret_cast<const float4*>(v + o + 4);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float gj = g[j] * gs;
+      mm[j] = beta1 * mm[j] + (1.f - beta1) * gj;
+      vv[j] = beta2 * vv[j] + (1.f - beta2) * gj * gj;
+      const float denom = sqrtf(vv[j]) * inv_sqrt_bc2 + eps;
+      p[j] = p[j] * (1.f - lr * wd) - lr * inv_bc1 * (mm[j] / denom);
+    }
+    *reinterpret_cast<float4*>(master + o) = *reinterpret_cast<float4*>(p);
+    *reinterpret_cast<float4*>(master + o + 4) = *reinterpret_cast<float4*>(p + 4);
+    *reinterpret_cast<float4*>(m + o) = *reinterpret_cast<float4*>(mm);
+    *reinterpret_cast<float4*>(m + o + 4) = *reinterpret_cast<float4*>(mm + 4);
+    *reinterpret_cast<float4*>(v + o) = *reinterpret_cast<float4*>(vv);
+    *reinterpret_cast<float4*>(v + o + 4) = *reinterpret_cast<float4*>(vv + 4);
+    if (param != nullptr) st8(param + o, pack8(p));
+  }
+  // tail (n % 8) handled by the first threads of block 0
+  if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+    const int64_t o = (nvec << 3) + threadIdx.x;
+    float gj = (kGradF32 ? ((const float*)grad)[o] : __bfloat162float(((const bf16*)grad)[o])) * gs;
+    float mj = beta1 * m[o] + (1.f - beta1) * gj;
+    float vj = beta2 * v[o] + (1.f - beta2) * gj * gj;
+    float pj = master[o] * (1.f - lr * wd) - lr * inv_bc1 * (mj / (sqrtf(vj) * inv_sqrt_bc2 + eps));
+    m[o] = mj;
+    v[o] = vj;
+    master[o] = pj;
+    if (param != nullptr) param[o] = __float2bfloat16(pj);
+  }
+}
+
+template <bool kF32>
+__global__ void __launch_bounds__(kSumsqThreads)
+sumsq_partial_kernel(const void* __restrict__ x, int64_t n, float* __restrict__ partials) {
+  __shared__ float red[33];
+  float acc = 0.f;
+  if (kF32) {
+    const int64_t nvec = n >> 2;
+    const float4* p = reinterpret_cast<const float4*>(x);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+      const float4 t = p[i];
+      acc += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+      const float t = ((const float*)x)[(nvec << 2) + threadIdx.x];
+      acc += t * t;
+    }
+  } else {
+    const int64_t nvec = n >> 3;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+      float f[8];
+      unpack8(ld8_stream((const bf16*)x + i * 8), f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc += f[j] * f[j];
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+      const float t = __bfloat162float(((const bf16*)x)[(nvec << 3) + threadIdx.x]);
+      acc += t * t;
+    }
+  }
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+}
+
+// deterministic final reduce of the per-block partials (single block)
+__global__ void __launch_bounds__(1024)
+sumsq_final_kernel(const float* __restrict__ partials, int nblocks, float* __restrict__ out, int accumulate) {
+  __shared__ float red[33];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < nblocks; i += blockDim.x) acc += partials[i];
+  acc = block_sum(acc, red);
+  if (threadIdx.x == 0) out[0] = accumulate ? out[0] + acc : acc;
+}
+
+__global__ void clip_coef_kernel(const float* __restrict__ sumsq, float max_norm, float* __restrict__ coef,
+                                 float* __restrict__ norm_out) {
+  const float norm = sqrtf(sumsq[0]);
+  if (norm_out != nullptr) norm_out[0] = norm;
+  float c = 1.f;
+  if (max_norm > 0.f) c = fminf(1.f, max_norm / (norm + 1e-6f));
+  if (!(norm == norm) || isinf(norm)) c = 0.f;  // non-finite gradients: skip the update
+  coef[0] = c;
+}
+
+template <typename S, typename D>
+__global__ void cast_kernel(const S* __restrict__ src, D* __restrict__ dst, int64_t n, float scale) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float v;
+    if constexpr (sizeof(S) == 4) v = (float)src[i]; else v = __bfloat162float(src[i]);
+    v *= scale;
+    if constexpr (sizeof(D) == 4) dst[i] = v; else dst[i] = __float2bfloat16(v);
+  }
+}
+
+}  // namespace dla
+
+using namespace dla;
+
+extern "C" {
+
+int dla_sumsq_blocks(void) { return kSumsqBlocks; }
+
+int dla_adamw(float* master, float* m, float* v, const void* grad, void* param, int64_t n, float lr, float beta1,
+              float beta2, float eps, float weight_decay, float bias_c1, float bias_c2,
+              const float* grad_scale_dev, float grad_prescale, int grad_is_fp32, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(bias_c1 > 0.f && bias_c2 > 0.f, DLA_E_BADARG, "adamw: bias corrections must be > 0");
+  if (n == 0) return 0;
+  int64_t blocks = ((n >> 3) + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
+  const float inv_bc1 = 1.f / bias_c1, inv_sqrt_bc2 = 1.f / sqrtf(bias_c2);
+  if (grad_is_fp32)
+    adamw_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(master, m, v, grad, (bf16*)param, n, lr, beta1, beta2, eps,
+                                                                     weight_decay, inv_bc1, inv_sqrt_bc2, grad_scale_dev, grad_prescale);
+  else
+    adamw_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(master, m, v, grad, (bf16*)param, n, lr, beta1, beta2, eps,
+                                                                      weight_decay, inv_bc1, inv_sqrt_bc2, grad_scale_dev, grad_prescale);
+  return check_launch("adamw");
+}
+
+int dla_sumsq(const void* x, int64_t n, int is_fp32, float* scratch, float* out, int accumulate, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(scratch != nullptr && out != nullptr, DLA_E_BADARG, "sumsq: scratch and out are required");
+  const int per = is_fp32 ? 4 : 8;
+  int64_t blocks = ((n / per) + kSumsqThreads - 1) / kSumsqThreads;
+  if (blocks < 1) blocks = 1;
+  if (blocks > kSumsqBlocks) blocks = kSumsqBlocks;
+  if (is_fp32)
+    sumsq_partial_kernel<true><<<(int)blocks, kSumsqThreads, 0, (cudaStream_t)stream>>>(x, n, scratch);
+  else
+    sumsq_partial_kernel<false><<<(int)blocks, kSumsqThreads, 0, (cudaStream_t)stream>>>(x, n, scratch);
+  int rc = check_launch("sumsq.partial");
+  if (rc) return rc;
+  sumsq_final_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(scratch, (int)blocks, out, accumulate);
+  return check_launch("sumsq.final");
+}
+
+int dla_clip_coef(const float* sumsq, float max_norm, float* coef_out, float* norm_out, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  clip_coef_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(sumsq, max_norm, coef_out, norm_out);
+  return check_launch("clip_coef");
+}
+
+int dla_cast(const void* src, void* dst, int64_t n, int src_is_fp32, int dst_is_fp32, float scale, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  if (n == 0) return 0;
+  int64_t blocks = (n + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (src_is_fp32 && dst_is_fp32) cast_kernel<float, float><<<(int)blocks, 256, 0, s>>>((const float*)src, (float*)dst, n, scale);
+  else if (src_is_fp32) cast_kernel<float, bf16><<<(int)blocks, 256, 0, s>>>((const float*)src, (bf16*)dst, n, scale);
+  else if (dst_is_fp32) cast_kernel<bf16, float><<<(int)blocks, 256, 0, s>>>((const bf16*)src, (float*)dst, n, scale);
+  else cast_kernel<bf16, bf16><<<(int)blocks, 256, 0, s>>>((const bf16*)src, (bf16*)dst, n, scale);
+  return check_launch("cast");
+}
+
+}  // extern "C"

@@ -1,0 +1,621 @@
+"""Differentiable ops.  CUDA tensors run the hand-written sm_100a kernels through
+:mod:`dla_b200.ops.native`; CPU tensors run the PyTorch restatements in
+:mod:`dla_b200.ops.reference` (used by the gloo plumbing tests and as the numerics oracle).
+There is no third path: a CUDA tensor without the native library raises.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional, Tuple
+
+import torch
+from torch.autograd import Function
+
+from dla_b200.ops import native as N
+from dla_b200.ops import reference as R
+
+BF16 = torch.bfloat16
+
+
+def _s(t: torch.Tensor) -> int:
+    return N.stream_ptr(t.device)
+
+
+def _c(t: torch.Tensor) -> torch.Tensor:
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _check_bf16(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and t.dtype != BF16:
+            raise TypeError(f"native kernels take bf16 tensors, got {t.dtype}")
+
+
+# =======================================================================================
+# GEMM
+# =======================================================================================
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = BF16, accumulate: bool = False) -> torch.Tensor:
+    """``C[M,N] (+)= op(A) @ op(B)^T`` on the tcgen05 kernel.
+
+    ``a``: ``[M, K]`` (or ``[K, M]`` when ``a_mn``), ``b``: ``[N, K]`` (or ``[K, N]`` when ``b_mn``); both
+    2-D with unit inner stride.  Shapes the TMA path cannot address (K or a pitch not a multiple
+    of 8, unaligned base) go to torch.matmul — a plain library GEMM, used only for odd shapes.
+    """
+    assert a.dim() == 2 and b.dim() == 2
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    Nn, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert K == Kb, f"gemm: inner dims differ ({K} vs {Kb})"
+    if a.stride(1) != 1:
+        a = a.contiguous()
+    if b.stride(1) != 1:
+        b = b.contiguous()
+    if out is None:
+        out = torch.empty(M, Nn, dtype=out_dtype, device=a.device)
+        accumulate = False
+    ok = (a.is_cuda and a.dtype == BF16 and b.dtype == BF16 and K % 8 == 0 and a.stride(0) % 8 == 0
+          and b.stride(0) % 8 == 0 and a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0
+          and out.stride(1) == 1 and out.dtype in (BF16, torch.float32)
+          and (not a_mn or M % 8 == 0) and (not b_mn or Nn % 8 == 0))
+    if not ok:
+        if a.is_cuda and a.dtype == BF16:
+            _note_fallback("gemm", (M, Nn, K))
+        am = a.t() if a_mn else a
+        bm = b if b_mn else b.t()
+        res = torch.matmul(am.to(torch.float32) if not a.is_cuda else am, bm.to(torch.float32) if not a.is_cuda else bm)
+        if accumulate:
+            out.add_(res.to(out.dtype))
+        else:
+            out.copy_(res.to(out.dtype))
+        return out
+    N.call("dla_gemm_bf16", N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, a.stride(0), b.stride(0), out.stride(0),
+           int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), _s(a))
+    return out
+
+
+_FALLBACKS: dict = {}
+
+
+def _note_fallback(op: str, shape) -> None:
+    key = (op, tuple(shape))
+    if key not in _FALLBACKS:
+        _FALLBACKS[key] = 0
+        import warnings
+        warnings.warn(f"{op}{tuple(shape)} is not TMA-addressable; using the library GEMM for this shape")
+    _FALLBACKS[key] += 1
+
+
+class _Linear(Function):
+    """``y = x @ w^T (+ b)``; dgrad and wgrad reuse the same tcgen05 kernel with MN-major operands.
+    If the weight carries ``_grad_slot`` (a view into the engine's flat gradient bucket) the wgrad
+    GEMM accumulates straight into it and autograd sees no weight gradient."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        x2 = x.reshape(-1, x.shape[-1])
+        y = gemm(x2, w)
+        if bias is not None:
+            N.call("dla_add_bias", N.ptr(y), None, N.ptr(bias), N.ptr(y), y.shape[0], y.shape[1], _s(y))
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias = bias is not None
+        ctx.bias_ref = bias
+        ctx.wref = w
+        ctx.xshape = x.shape
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w = ctx.saved_tensors
+        dy2 = _c(dy.reshape(-1, dy.shape[-1]))
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, w, b_mn=True).view(ctx.xshape)
+        if ctx.needs_input_grad[1]:
+            slot = getattr(ctx.wref, "_grad_slot", None)
+            if slot is not None:
+                gemm(dy2, x2, a_mn=True, b_mn=True, out=slot, accumulate=True)
+            else:
+                dw = gemm(dy2, x2, a_mn=True, b_mn=True)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            b = ctx.bias_ref
+            slot = getattr(b, "_grad_slot", None)
+            H = dy2.shape[1]
+            scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * H * 4, dy2.device)
+            if slot is not None:
+                N.call("dla_bias_grad", N.ptr(dy2), N.ptr(slot), N.ptr(scratch), 1, dy2.shape[0], H, _s(dy2))
+            else:
+                db = torch.empty(H, dtype=BF16, device=dy2.device)
+                N.call("dla_bias_grad", N.ptr(dy2), N.ptr(db), N.ptr(scratch), 0, dy2.shape[0], H, _s(dy2))
+        return dx, dw, db
+
+
+def linear(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if not x.is_cuda:
+        return R.linear(x, w, bias)
+    _check_bf16(x, w, bias)
+    return _Linear.apply(x, w, bias)
+
+
+# =======================================================================================
+# norms
+# =======================================================================================
+
+class _AddRMSNorm(Function):
+    @staticmethod
+    def forward(ctx, x, delta, w, eps):
+        H = x.shape[-1]
+        x2 = _c(x.reshape(-1, H))
+        M = x2.shape[0]
+        y = torch.empty_like(x2)
+        rstd = torch.empty(M, dtype=torch.float32, device=x.device)
+        if delta is not None:
+            d2 = _c(delta.reshape(-1, H))
+            resid = torch.empty_like(x2)
+            N.call("dla_rmsnorm_fwd", N.ptr(x2), N.ptr(d2), N.ptr(w), N.ptr(resid), N.ptr(y), N.ptr(rstd), M, H, eps, _s(x))
+        else:
+            resid = x2
+            N.call("dla_rmsnorm_fwd", N.ptr(x2), None, N.ptr(w), None, N.ptr(y), N.ptr(rstd), M, H, eps, _s(x))
+        ctx.save_for_backward(resid, w, rstd)
+        ctx.has_delta = delta is not None
+        ctx.shape = x.shape
+        ctx.wref = w
+        return resid.view(x.shape), y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dresid, dy):
+        resid, w, rstd = ctx.saved_tensors
+        M, H = resid.shape
+        dy2 = _c(dy.reshape(M, H)) if dy is not None else torch.zeros_like(resid)
+        dr2 = _c(dresid.reshape(M, H)) if dresid is not None else None
+        dx = torch.empty_like(resid)
+        scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * H * 4, resid.device)
+        slot = getattr(ctx.wref, "_grad_slot", None)
+        dw = None
+        need_w = ctx.needs_input_grad[2]
+        if need_w and slot is None:
+            dw = torch.empty(H, dtype=BF16, device=resid.device)
+        tgt = slot if slot is not None else dw
+        N.call("dla_rmsnorm_bwd", N.ptr(dy2), N.ptr(resid), N.ptr(w), N.ptr(rstd), N.ptr(dr2), N.ptr(dx),
+               N.ptr(tgt) if need_w else None, N.ptr(scratch), int(slot is not None), M, H, _s(resid))
+        dxv = dx.view(ctx.shape)
+        return dxv, (dxv if ctx.has_delta else None), dw, None
+
+
+def add_rmsnorm(x: torch.Tensor, delta: Optional[torch.Tensor], w: torch.Tensor, eps: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``resid = x + delta`` (or ``x``), ``y = rmsnorm(resid) * w``; returns ``(resid, y)``."""
+    if not x.is_cuda:
+        resid = x if delta is None else x + delta
+        return resid, R.rmsnorm(resid, w, eps)
+    _check_bf16(x, delta, w)
+    return _AddRMSNorm.apply(x, delta, w, eps)
+
+
+def rmsnorm(x: torch.Tensor, w: torch.Tensor, eps: float) -> torch.Tensor:
+    return add_rmsnorm(x, None, w, eps)[1]
+
+
+class _LayerNorm(Function):
+    @staticmethod
+    def forward(ctx, x, w, b, eps):
+        H = x.shape[-1]
+        x2 = _c(x.reshape(-1, H))
+        M = x2.shape[0]
+        y = torch.empty_like(x2)
+        stats = torch.empty(2 * M, dtype=torch.float32, device=x.device)
+        N.call("dla_layernorm_fwd", N.ptr(x2), N.ptr(w), N.ptr(b), N.ptr(y), N.ptr(stats), M, H, eps, _s(x))
+        ctx.save_for_backward(x2, w, stats)
+        ctx.refs = (w, b)
+        ctx.shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, stats = ctx.saved_tensors
+        M, H = x2.shape
+        dy2 = _c(dy.reshape(M, H))
+        dx = torch.empty_like(x2)
+        scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * 2 * H * 4, x2.device)
+        wref, bref = ctx.refs
+        wslot = getattr(wref, "_grad_slot", None)
+        bslot = getattr(bref, "_grad_slot", None) if bref is not None else None
+        use_slots = wslot is not None and (bref is None or bslot is not None)
+        dw = wslot if use_slots else torch.empty(H, dtype=BF16, device=x2.device)
+        db = None
+        if bref is not None:
+            db = bslot if use_slots else torch.empty(H, dtype=BF16, device=x2.device)
+        N.call("dla_layernorm_bwd", N.ptr(dy2), N.ptr(x2), N.ptr(w), N.ptr(stats), N.ptr(dx), N.ptr(dw), N.ptr(db),
+               N.ptr(scratch), int(use_slots), M, H, _s(x2))
+        if use_slots:
+            return dx.view(ctx.shape), None, None, None
+        return dx.view(ctx.shape), dw, db, None
+
+
+def layernorm(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], eps: float) -> torch.Tensor:
+    if not x.is_cuda:
+        return R.layernorm(x, w, b, eps)
+    _check_bf16(x, w, b)
+    return _LayerNorm.apply(x, w, b, eps)
+
+
+# =======================================================================================
+# RoPE on packed QKV
+# =======================================================================================
+_ROPE_TABLES: dict = {}
+
+
+def rope_tables(max_pos: int, rot_dim: int, theta: float, device: torch.device) -> Tuple[torch.Tensor, torch.Tensor]:
+    key = (max_pos, rot_dim, float(theta), str(device))
+    if key not in _ROPE_TABLES:
+        cos, sin = R.rope_tables(torch.arange(max_pos, device=device), rot_dim, theta)
+        _ROPE_TABLES[key] = (cos.contiguous(), sin.contiguous())
+    return _ROPE_TABLES[key]
+
+
+class _RopeQKV(Function):
+    """In-place RoPE on the q and k heads of a packed ``[M, (Hq + 2 Hk) * D]`` projection."""
+
+    @staticmethod
+    def forward(ctx, qkv, positions, cos, sin, n_rot_heads, head_dim, rot_dim):
+        M = qkv.shape[0]
+        N.call("dla_rope_inplace", N.ptr(qkv), N.ptr(cos), N.ptr(sin), N.ptr(positions), M, n_rot_heads, head_dim,
+               rot_dim, qkv.stride(0), 1.0, _s(qkv))
+        ctx.mark_dirty(qkv)
+        ctx.save_for_backward(positions, cos, sin)
+        ctx.meta = (n_rot_heads, head_dim, rot_dim)
+        return qkv
+
+    @staticmethod
+    def backward(ctx, g):
+        positions, cos, sin = ctx.saved_tensors
+        n_rot_heads, head_dim, rot_dim = ctx.meta
+        g = g.clone(memory_format=torch.contiguous_format)
+        N.call("dla_rope_inplace", N.ptr(g), N.ptr(cos), N.ptr(sin), N.ptr(positions), g.shape[0], n_rot_heads,
+               head_dim, rot_dim, g.stride(0), -1.0, _s(g))
+        return g, None, None, None, None, None, None
+
+
+def rope_qkv(qkv: torch.Tensor, positions: torch.Tensor, n_q: int, n_kv: int, head_dim: int, theta: float,
+             rot_dim: Optional[int] = None, max_pos: int = 8192) -> torch.Tensor:
+    """Applies RoPE to the q and k parts of packed ``qkv [M, (n_q + 2 n_kv) * D]``; ``positions [M]``."""
+    rd = rot_dim or head_dim
+    if not qkv.is_cuda:
+        M = qkv.shape[0]
+        q, k, v = qkv.split([n_q * head_dim, n_kv * head_dim, n_kv * head_dim], dim=-1)
+        q = R.rope(q.reshape(1, M, n_q, head_dim), positions.reshape(1, M), theta, rd).reshape(M, -1)
+        k = R.rope(k.reshape(1, M, n_kv, head_dim), positions.reshape(1, M), theta, rd).reshape(M, -1)
+        return torch.cat([q, k, v], dim=-1)
+    cos, sin = rope_tables(max_pos, rd, theta, qkv.device)
+    pos32 = positions.to(torch.int32)
+    return _RopeQKV.apply(qkv, pos32, cos, sin, n_q + n_kv, head_dim, rd)
+
+
+# =======================================================================================
+# activations
+# =======================================================================================
+
+class _SwiGLU(Function):
+    @staticmethod
+    def forward(ctx, gu):
+        F2 = gu.shape[-1]
+        g2 = _c(gu.reshape(-1, F2))
+        h = torch.empty(g2.shape[0], F2 // 2, dtype=gu.dtype, device=gu.device)
+        N.call("dla_swiglu_fwd", N.ptr(g2), N.ptr(h), g2.shape[0], F2 // 2, _s(gu))
+        ctx.save_for_backward(g2)
+        ctx.shape = gu.shape
+        return h.view(*gu.shape[:-1], F2 // 2)
+
+    @staticmethod
+    def backward(ctx, dh):
+        (g2,) = ctx.saved_tensors
+        d2 = _c(dh.reshape(g2.shape[0], -1))
+        dgu = torch.empty_like(g2)
+        N.call("dla_swiglu_bwd", N.ptr(d2), N.ptr(g2), N.ptr(dgu), g2.shape[0], g2.shape[1] // 2, _s(g2))
+        return dgu.view(ctx.shape)
+
+
+def swiglu(gu: torch.Tensor) -> torch.Tensor:
+    if not gu.is_cuda:
+        return R.swiglu(gu)
+    _check_bf16(gu)
+    return _SwiGLU.apply(gu)
+
+
+class _GeluBias(Function):
+    @staticmethod
+    def forward(ctx, x, bias):
+        Fd = x.shape[-1]
+        x2 = _c(x.reshape(-1, Fd))
+        y = torch.empty_like(x2)
+        N.call("dla_gelu_fwd", N.ptr(x2), N.ptr(bias), N.ptr(y), x2.shape[0], Fd, _s(x))
+        ctx.save_for_backward(x2, bias) if bias is not None else ctx.save_for_backward(x2)
+        ctx.has_bias = bias is not None
+        ctx.bias_ref = bias
+        ctx.shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        saved = ctx.saved_tensors
+        x2 = saved[0]
+        bias = saved[1] if ctx.has_bias else None
+        d2 = _c(dy.reshape(x2.shape))
+        dx = torch.empty_like(x2)
+        N.call("dla_gelu_bwd", N.ptr(d2), N.ptr(x2), N.ptr(bias), N.ptr(dx), x2.shape[0], x2.shape[1], _s(x2))
+        db = None
+        if ctx.has_bias and ctx.needs_input_grad[1]:
+            H = x2.shape[1]
+            scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * H * 4, x2.device)
+            slot = getattr(ctx.bias_ref, "_grad_slot", None)
+            if slot is not None:
+                N.call("dla_bias_grad", N.ptr(dx), N.ptr(slot), N.ptr(scratch), 1, x2.shape[0], H, _s(x2))
+            else:
+                db = torch.empty(H, dtype=BF16, device=x2.device)
+                N.call("dla_bias_grad", N.ptr(dx), N.ptr(db), N.ptr(scratch), 0, x2.shape[0], H, _s(x2))
+        return dx.view(ctx.shape), db
+
+
+def gelu_bias(x: torch.Tensor, bias: Optional[torch.Tensor]) -> torch.Tensor:
+    """tanh-GELU of ``x + bias`` (GPT-2's ``gelu_new``)."""
+    if not x.is_cuda:
+        return R.gelu_tanh(x if bias is None else x + bias)
+    _check_bf16(x, bias)
+    return _GeluBias.apply(x, bias)
+
+
+# =======================================================================================
+# embedding
+# =======================================================================================
+
+class _Embedding(Function):
+    @staticmethod
+    def forward(ctx, ids, table, pos_table, T):
+        flat = _c(ids.reshape(-1))
+        M, (V, H) = flat.numel(), table.shape
+        out = torch.empty(M, H, dtype=table.dtype, device=table.device)
+        N.call("dla_embedding_fwd", N.ptr(flat), N.ptr(table), N.ptr(pos_table), N.ptr(out), M, H, V, T, _s(table))
+        ctx.save_for_backward(flat)
+        ctx.refs = (table, pos_table)
+        ctx.meta = (M, H, V, T)
+        return out.view(*ids.shape, H)
+
+    @staticmethod
+    def backward(ctx, dout):
+        (flat,) = ctx.saved_tensors
+        M, H, V, T = ctx.meta
+        table, pos_table = ctx.refs
+        d2 = _c(dout.reshape(M, H))
+        tslot = getattr(table, "_grad_slot", None)
+        pslot = getattr(pos_table, "_grad_slot", None) if pos_table is not None else None
+        dt = tslot if tslot is not None else torch.zeros(V, H, dtype=BF16, device=d2.device)
+        dp = None
+        if pos_table is not None:
+            dp = pslot if pslot is not None else torch.zeros_like(pos_table)
+        N.call("dla_embedding_bwd", N.ptr(flat), N.ptr(d2), N.ptr(dt), N.ptr(dp), M, H, V, T, _s(d2))
+        return None, (None if tslot is not None else dt), (None if (pos_table is None or pslot is not None) else dp), None
+
+
+def embedding(ids: torch.Tensor, table: torch.Tensor, pos_table: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Token (+ learned position, GPT-2) embedding; ``ids [B, T]``."""
+    if not table.is_cuda:
+        out = torch.nn.functional.embedding(ids, table)
+        if pos_table is not None:
+            out = out + pos_table[: ids.shape[-1]]
+        return out
+    _check_bf16(table, pos_table)
+    return _Embedding.apply(ids, table, pos_table, ids.shape[-1])
+
+
+# =======================================================================================
+# attention
+# =======================================================================================
+
+class _Attention(Function):
+    @staticmethod
+    def forward(ctx, q, k, v, seqlens, causal, scale):
+        B, T, Hq, D = q.shape
+        Hk = k.shape[2]
+        o = torch.empty(B, T, Hq, D, dtype=q.dtype, device=q.device)
+        lse = torch.empty(B, Hq, T, dtype=torch.float32, device=q.device)
+        N.call("dla_attn_fwd", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(lse), B, T, Hq, Hk, D,
+               q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), scale, int(causal), _s(q))
+        ctx.save_for_backward(q, k, v, o, lse, seqlens) if seqlens is not None else ctx.save_for_backward(q, k, v, o, lse)
+        ctx.has_len = seqlens is not None
+        ctx.meta = (causal, scale)
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        saved = ctx.saved_tensors
+        q, k, v, o, lse = saved[:5]
+        seqlens = saved[5] if ctx.has_len else None
+        causal, scale = ctx.meta
+        B, T, Hq, D = q.shape
+        Hk = k.shape[2]
+        do = _c(do)
+        # gradients are produced in one packed [B, T, Hq + 2 Hk, D] buffer so that, when q/k/v were
+        # views of one fused projection, autograd's view backward concatenates without extra copies
+        dqkv = torch.empty(B, T, Hq + 2 * Hk, D, dtype=q.dtype, device=q.device)
+        dq, dk, dv = dqkv[:, :, :Hq], dqkv[:, :, Hq:Hq + Hk], dqkv[:, :, Hq + Hk:]
+        dq_acc = torch.empty(B, T, Hq, D, dtype=torch.float32, device=q.device)
+        delta = torch.empty(B, Hq, T, dtype=torch.float32, device=q.device)
+        assert do.stride(2) == o.stride(2) and do.stride(1) == o.stride(1) and do.stride(0) == o.stride(0)
+        N.call("dla_attn_bwd", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
+               N.ptr(dq), N.ptr(dk), N.ptr(dv), N.ptr(dq_acc), N.ptr(delta), B, T, Hq, Hk, D,
+               q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), scale, int(causal), _s(q))
+        return dq, dk, dv, None, None, None
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, seqlens: Optional[torch.Tensor] = None,
+              causal: bool = True, scale: Optional[float] = None,
+              segment_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Causal GQA attention on ``[B, T, H, D]`` tensors (views of a packed QKV are fine: strides are
+    passed through).  ``seqlens [B]`` int32 masks right padding."""
+    scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
+    if not q.is_cuda or segment_ids is not None:
+        return R.attention(q, k, v, causal=causal, seqlens=seqlens, scale=scale, segment_ids=segment_ids)
+    _check_bf16(q, k, v)
+    if seqlens is not None:
+        seqlens = seqlens.to(torch.int32)
+    return _Attention.apply(q, k, v, seqlens, causal, scale)
+
+
+# =======================================================================================
+# fused lm_head -> per-token log-prob
+# =======================================================================================
+LOGPROB_BWD_CHUNK = 2048
+
+
+class _LinearLogprob(Function):
+    """``logp[m] = log_softmax(h[m] @ W^T)[label[m]]`` without materialising ``[M, V]``.
+
+    Forward: tcgen05 GEMM whose epilogue reduces every 128x256 logits tile to (max, sumexp, picked).
+    Backward: per row-chunk, recompute bf16 logits with the GEMM, turn them into
+    ``g * (onehot - softmax)`` in place, and feed two more GEMMs (dgrad, wgrad)."""
+
+    @staticmethod
+    def forward(ctx, h, w, labels):
+        M, K = h.shape
+        V = w.shape[0]
+        nbytes = int(N.load().dla_lmhead_scratch_bytes(M, V))
+        scratch = N.workspace("lmhead", nbytes, h.device)
+        logp = torch.empty(M, dtype=torch.float32, device=h.device)
+        lse = torch.empty(M, dtype=torch.float32, device=h.device)
+        N.call("dla_lmhead_logprob", N.ptr(h), N.ptr(w), N.ptr(labels), M, V, K, h.stride(0), w.stride(0),
+               N.ptr(scratch), N.ptr(logp), N.ptr(lse), _s(h))
+        ctx.save_for_backward(h, w, labels, lse)
+        ctx.wref = w
+        return logp, lse
+
+    @staticmethod
+    def backward(ctx, g, _g_lse):
+        h, w, labels, lse = ctx.saved_tensors
+        M, K = h.shape
+        V = w.shape[0]
+        g = _c(g.float())
+        dh = torch.empty_like(h) if ctx.needs_input_grad[0] else None
+        slot = getattr(ctx.wref, "_grad_slot", None)
+        dw = None
+        if ctx.needs_input_grad[1] and slot is None:
+            dw = torch.zeros_like(w)
+        wtgt = slot if slot is not None else dw
+        Vp = (V + 7) // 8 * 8
+        chunk = min(LOGPROB_BWD_CHUNK, M)
+        buf = N.workspace("lmhead_bwd", chunk * Vp * 2, h.device).view(BF16)[: chunk * Vp].view(chunk, Vp)
+        for s in range(0, M, chunk):
+            e = min(s + chunk, M)
+            n = e - s
+            dl = buf[:n].narrow(1, 0, V)            # [n, V] view, row pitch Vp
+            gemm(h[s:e], w, out=dl)                  # recompute bf16 logits for this row chunk
+            N.call("dla_logprob_grad_inplace", N.ptr(buf), N.ptr(lse[s:e]), N.ptr(labels[s:e]), N.ptr(g[s:e]),
+                   n, V, Vp, _s(h))
+            if dh is not None:
+                gemm(dl, w, b_mn=True, out=dh[s:e])
+            if wtgt is not None:
+                gemm(dl, h[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=True)
+        return dh, dw, None
+
+
+def linear_logprob(h: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Per-token label log-prob and log-sum-exp (fp32 ``[M]``) of ``h [M, K] @ w[V, K]^T``.
+    Labels < 0 are ignored (log-prob 0, no gradient)."""
+    if not h.is_cuda:
+        return R.token_logprobs(h, w, labels)
+    _check_bf16(h, w)
+    return _LinearLogprob.apply(_c(h), w, _c(labels.to(torch.int64)))
+
+
+# =======================================================================================
+# sequence reductions and losses
+# =======================================================================================
+
+class _SeqMean(Function):
+    @staticmethod
+    def forward(ctx, tok, mask, use_sum):
+        B, T = tok.shape
+        tok, mask = _c(tok.float()), _c(mask.to(torch.int64))
+        out = torch.empty(B, dtype=torch.float32, device=tok.device)
+        N.call("dla_seq_mean_fwd", N.ptr(tok), N.ptr(mask), N.ptr(out), B, T, int(use_sum), _s(tok))
+        ctx.save_for_backward(mask)
+        ctx.meta = (B, T, use_sum)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (mask,) = ctx.saved_tensors
+        B, T, use_sum = ctx.meta
+        g = _c(g.float())
+        dtok = torch.empty(B, T, dtype=torch.float32, device=g.device)
+        N.call("dla_seq_mean_bwd", N.ptr(g), N.ptr(mask), N.ptr(dtok), B, T, int(use_sum), _s(g))
+        return dtok, None, None
+
+
+def sequence_logprob(token_logp: torch.Tensor, mask: torch.Tensor, reduction: str = "mean") -> torch.Tensor:
+    """Per-sequence masked mean (reference semantics, ``R/src/training/train_dpo.py:38``) or sum."""
+    if not token_logp.is_cuda:
+        if reduction == "sum":
+            return (token_logp * mask.to(token_logp.dtype)).sum(1)
+        return R.sequence_mean_logprob(token_logp, mask)
+    return _SeqMean.apply(token_logp, mask, reduction == "sum")
+
+
+class _DPOLoss(Function):
+    @staticmethod
+    def forward(ctx, pp, pn, rp, rn, beta, ls, scale):
+        B = pp.numel()
+        pp, pn, rp, rn = (_c(t.float()) for t in (pp, pn, rp, rn))
+        out = torch.empty(3, dtype=torch.float32, device=pp.device)
+        dpp = torch.empty(B, dtype=torch.float32, device=pp.device)
+        dpn = torch.empty(B, dtype=torch.float32, device=pp.device)
+        N.call("dla_dpo_loss", N.ptr(pp), N.ptr(pn), N.ptr(rp), N.ptr(rn), B, beta, ls, scale, N.ptr(out),
+               N.ptr(dpp), N.ptr(dpn), _s(pp))
+        ctx.save_for_backward(dpp, dpn)
+        return out[0], out[1:].detach()
+
+    @staticmethod
+    def backward(ctx, g, _gs):
+        dpp, dpn = ctx.saved_tensors
+        return dpp * g, dpn * g, None, None, None, None, None
+
+
+def dpo_loss(pol_pos, pol_neg, ref_pos, ref_neg, beta: float, label_smoothing: float = 0.0,
+             scale: Optional[float] = None):
+    """Returns ``(loss, stats)`` with ``stats = [preference_rate, mean_margin]``.  ``scale`` defaults to
+    ``1/B`` (batch mean, ``R/src/training/train_dpo.py:44``)."""
+    B = pol_pos.numel()
+    scale = 1.0 / B if scale is None else scale
+    if not pol_pos.is_cuda:
+        z = beta * ((pol_pos - pol_neg) - (ref_pos - ref_neg))
+        loss = R.dpo_loss(pol_pos, pol_neg, ref_pos, ref_neg, beta, label_smoothing) * (scale * B)
+        stats = torch.stack([(pol_pos > pol_neg).float().sum() * scale, z.detach().sum() * scale])
+        return loss, stats
+    return _DPOLoss.apply(pol_pos, pol_neg, ref_pos.detach(), ref_neg.detach(), beta, label_smoothing, scale)
+
+
+class _PairwiseLoss(Function):
+    @staticmethod
+    def forward(ctx, c, r, scale):
+        B = c.numel()
+        c, r = _c(c.float()), _c(r.float())
+        out = torch.empty(2, dtype=torch.float32, device=c.device)
+        dc = torch.empty(B, dtype=torch.float32, device=c.device)
+        dr = torch.empty(B, dtype=torch.float32, device=c.device)
+        N.call("dla_pairwise_loss", N.ptr(c), N.ptr(r), B, scale, N.ptr(out), N.ptr(dc), N.ptr(dr), _s(c))
+        ctx.save_for_backward(dc, dr)
+        return out[0], out[1].detach()
+
+    @staticmethod
+    def backward(ctx, g, _ga):
+        dc, dr = ctx.saved_tensors
+        return dc * g, dr * g, None
+
+
+def pairwise_loss(chosen: torch.Tensor, rejected: torch.Tensor, scale: Optional[float] = None):
+    """Bradley-Terry loss; returns ``(loss, accuracy)`` (``R/src/models/reward_model.py:67-68``)."""
+    B = chosen.numel()
+    scale = 1.0 / B if scale is None else scale
+    if not chosen.is_cuda:
+        return R.pairwise_loss(chosen, rejected) * (scale * B), (chosen > rejected).float().sum() * scale
+    return _PairwiseLoss.apply(chosen, rejected, scale)

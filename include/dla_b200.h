@@ -1,0 +1,210 @@
+/*
+ * dla_b200 native library — C ABI of the sm_100a kernels.
+ *
+ * Conventions
+ *   - every entry point returns 0 on success, a cudaError_t (>0) or a negative DLA_E_* code on
+ *     failure; dla_last_error() returns a human-readable message for the calling thread.
+ *   - pointers are device pointers unless a comment says "host"; "bf16" buffers hold
+ *     __nv_bfloat16; strides/leading dimensions are in ELEMENTS.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Nothing here
+ *     synchronises the host; nothing allocates unless stated.
+ *   - "scratch" arguments are caller-provided global-memory work areas; their required sizes
+ *     come from the matching *_scratch_bytes() query.
+ *
+ * The reference framework (nikhil-lalgudi/distributed-llm-alignment, "R/") ships no native code;
+ * each declaration cites the Python line whose library kernels it replaces.
+ */
+#ifndef DLA_B200_H_
+#define DLA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DLA_E_BADARG   (-1)
+#define DLA_E_UNSUPP   (-2)
+#define DLA_E_DRIVER   (-3)
+#define DLA_E_TOOLARGE (-4)
+
+const char* dla_last_error(void);
+int dla_version(void);
+/* One process drives one GPU: tell the library which (call once after torch.cuda.set_device).  Every
+ * entry point binds that device to its calling thread, so autograd worker threads launch on it too. */
+int dla_set_device(int device);
+/* Number of kernel launches issued through this library since load (all threads). */
+long long dla_launch_count(void);
+
+/* ---------------------------------------------------------------- normalisation (K3) */
+/* y = rmsnorm(x [+ delta]) * w ; optionally writes resid_out = x + delta.  R: HF LlamaRMSNorm
+ * reached from R/src/training/train_dpo.py:32.  x,delta,resid_out,y: bf16 [M,H]; w: bf16 [H];
+ * rstd: fp32 [M].  delta/resid_out may be NULL. H % 8 == 0, H <= 16384. */
+int dla_rmsnorm_fwd(const void* x, const void* delta, const void* w, void* resid_out, void* y,
+                    float* rstd, int64_t M, int H, float eps, void* stream);
+/* dx = d(rmsnorm)/dx * dy [+ dresid]; dw += / = sum_rows(dy * xhat).  x is the normalised
+ * input (resid_out of fwd).  scratch: fp32 [dla_norm_bwd_blocks() * H] (2H per block for layernorm). */
+int dla_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd,
+                    const void* dresid, void* dx, void* dw, float* scratch, int accumulate_dw,
+                    int64_t M, int H, void* stream);
+int dla_norm_bwd_blocks(void);
+/* LayerNorm (GPT-2 / phi-2 family): y = (x-mean)*rstd*w + b. stats: fp32 [2*M] (mean, rstd). */
+int dla_layernorm_fwd(const void* x, const void* w, const void* b, void* y, float* stats,
+                      int64_t M, int H, float eps, void* stream);
+int dla_layernorm_bwd(const void* dy, const void* x, const void* w, const float* stats,
+                      void* dx, void* dw, void* db, float* scratch, int accumulate,
+                      int64_t M, int H, void* stream);
+
+/* ---------------------------------------------------------------- RoPE (K4) */
+/* In-place rotate-half RoPE on the first n_heads heads of each row of a packed [M, row_stride]
+ * bf16 buffer (q heads then k heads of a fused QKV projection).  cos/sin: fp32 [max_pos, rot_dim/2];
+ * positions: int32 [M].  sign=+1 forward, -1 backward (inverse rotation of the gradient). */
+int dla_rope_inplace(void* x, const float* cos_t, const float* sin_t, const int32_t* positions,
+                     int64_t M, int n_heads, int head_dim, int rot_dim, int64_t row_stride,
+                     float sign, void* stream);
+
+/* ---------------------------------------------------------------- activations (K5) */
+/* h = silu(gu[:, :F]) * gu[:, F:] ; gu bf16 [M, 2F], h bf16 [M, F]. */
+int dla_swiglu_fwd(const void* gu, void* h, int64_t M, int F, void* stream);
+int dla_swiglu_bwd(const void* dh, const void* gu, void* dgu, int64_t M, int F, void* stream);
+/* tanh-GELU with optional bias add fused: y = gelu(x + b). */
+int dla_gelu_fwd(const void* x, const void* bias, void* y, int64_t M, int F, void* stream);
+int dla_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, int64_t M, int F, void* stream);
+/* y = a + b (+ bias broadcast over rows) in bf16; used for residual / bias adds. */
+int dla_add_bias(const void* a, const void* b, const void* bias, void* y, int64_t M, int H, void* stream);
+/* db (bf16 [H]) (+)= column sums of dy [M,H]; scratch fp32 [dla_norm_bwd_blocks()*H]. */
+int dla_bias_grad(const void* dy, void* db, float* scratch, int accumulate, int64_t M, int H, void* stream);
+
+/* ---------------------------------------------------------------- embedding (K17) */
+int dla_embedding_fwd(const int64_t* ids, const void* table, const void* pos_table, void* out,
+                      int64_t M, int H, int V, int T, void* stream);
+/* dtable[ids[m]] += dout[m] (bf16x2 atomics); dpos_table likewise for learned positions. */
+int dla_embedding_bwd(const int64_t* ids, const void* dout, void* dtable, void* dpos_table,
+                      int64_t M, int H, int V, int T, void* stream);
+
+/* ---------------------------------------------------------------- optimizer (K13, K14) */
+/* Fused AdamW on a flat shard: reads bf16 grad, updates fp32 master/m/v, writes the bf16 param.
+ * grad_scale_dev (nullable): device fp32 scalar multiplied into the gradient (clip factor), so no
+ * host sync sits between the norm and the update.  R: torch.optim.AdamW at
+ * R/src/training/train_dpo.py:73-77,120. */
+int dla_adamw(float* master, float* m, float* v, const void* grad, void* param, int64_t n,
+              float lr, float beta1, float beta2, float eps, float weight_decay,
+              float bias_c1, float bias_c2, const float* grad_scale_dev, float grad_prescale,
+              int grad_is_fp32, void* stream);
+/* out[0] (+)= sum(x^2). scratch: fp32 [dla_sumsq_blocks()].  R: clip_grad_norm_ at
+ * R/src/training/utils.py:121-123. */
+int dla_sumsq(const void* x, int64_t n, int is_fp32, float* scratch, float* out, int accumulate,
+              void* stream);
+int dla_sumsq_blocks(void);
+/* coef = min(1, max_norm / (sqrt(sumsq) + 1e-6)); norm_out = sqrt(sumsq). */
+int dla_clip_coef(const float* sumsq, float max_norm, float* coef_out, float* norm_out, void* stream);
+int dla_cast(const void* src, void* dst, int64_t n, int src_is_fp32, int dst_is_fp32, float scale, void* stream);
+
+/* ---------------------------------------------------------------- losses (K8, K9, K11) */
+/* DPO sigmoid loss over B pairs with gradients wrt the policy log-probs and the preference
+ * rate, one launch.  out: fp32 [3] = {loss, preference_rate, mean_margin}; scale = 1/(global B).
+ * R: R/src/training/train_dpo.py:42-44,130-132. */
+int dla_dpo_loss(const float* pol_pos, const float* pol_neg, const float* ref_pos,
+                 const float* ref_neg, int B, float beta, float label_smoothing, float scale,
+                 float* out, float* dpol_pos, float* dpol_neg, void* stream);
+/* Bradley-Terry pairwise loss + grads + accuracy.  out fp32[2] = {loss, accuracy}.
+ * R: R/src/models/reward_model.py:67-68. */
+int dla_pairwise_loss(const float* chosen, const float* rejected, int B, float scale, float* out,
+                      float* dchosen, float* drejected, void* stream);
+/* per-sequence masked mean of token log-probs: seq[b] = sum_t(tok*mask)/max(sum mask,1);
+ * bwd: dtok = dseq[b]*mask/len.  R: R/src/training/train_dpo.py:38. */
+int dla_seq_mean_fwd(const float* tok, const int64_t* mask, float* seq, int B, int T, int sum_not_mean, void* stream);
+int dla_seq_mean_bwd(const float* dseq, const int64_t* mask, float* dtok, int B, int T, int sum_not_mean, void* stream);
+
+/* ---------------------------------------------------------------- GEMM (K1) */
+/* C[M,N] (+)= A[M,K] * B[N,K]^T with bf16 operands and fp32 accumulation in TMEM
+ * (tcgen05.mma, TMA-fed, persistent).  a_mn_major: A is stored [K, M] (M contiguous) instead of
+ * [M, K]; b_mn_major: B is stored [K, N] (N contiguous) instead of [N, K].  c_fp32 selects the
+ * output type; accumulate adds into C.  K % 8 == 0; lda/ldb % 8 == 0; pointers 16-byte aligned.
+ * R: nn.Linear -> cuBLASLt under R/src/training/train_dpo.py:32. */
+int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
+                  int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
+                  int c_fp32, int accumulate, void* stream);
+/* 0 = auto, 1 = 1-CTA 128x256, 2 = 2-CTA pair 256x256 (debug / benchmarking switch). */
+int dla_gemm_set_variant(int variant);
+
+/* ---------------------------------------------------------------- fused lm_head log-prob (K6, K7) */
+/* logp[m] = log_softmax(X[m,:] . W^T)[labels[m]], lse[m] = logsumexp — the [M,V] logits never
+ * reach memory: the GEMM epilogue reduces each 128x256 tile to (max, sumexp, picked) partials.
+ * scratch: dla_lmhead_scratch_bytes(M, V).  labels < 0 => logp = 0.
+ * R: R/src/training/train_dpo.py:31-39 (log_softmax + gather over the vocab). */
+int dla_lmhead_logprob(const void* X, const void* W, const int64_t* labels, int M, int V, int K,
+                       int64_t ldx, int64_t ldw, void* scratch, float* logp, float* lse,
+                       void* stream);
+size_t dla_lmhead_scratch_bytes(int M, int V);
+/* In place on a bf16 logits chunk [Mc, V]: logits <- grow[m] * (onehot(label) - softmax(logits)),
+ * using the saved lse (backward of the op above, chunked). */
+int dla_logprob_grad_inplace(void* logits, const float* lse, const int64_t* labels,
+                             const float* grow, int Mc, int V, int64_t ld, void* stream);
+
+/* ---------------------------------------------------------------- attention (K2, K16) */
+/* Causal GQA flash attention, tcgen05: q [B,T,Hq,D], k/v [B,T,Hk,D] bf16 with explicit element
+ * strides (batch, token, head); D == 128 or 64.  seqlens (nullable int32 [B]) masks right padding.
+ * lse: fp32 [B,Hq,T]. */
+int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse,
+                 int B, int T, int Hq, int Hk, int D,
+                 int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
+                 int64_t o_sb, int64_t o_st, int64_t o_sh,
+                 const int32_t* seqlens, float scale, int causal, void* stream);
+/* Backward. dq_acc: fp32 scratch [B,T,Hq,D] (zeroed inside); delta: fp32 scratch [B,Hq,T]. */
+int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                 const float* lse, void* dq, void* dk, void* dv, float* dq_acc, float* delta,
+                 int B, int T, int Hq, int Hk, int D,
+                 int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
+                 int64_t o_sb, int64_t o_st, int64_t o_sh,
+                 const int32_t* seqlens, float scale, int causal, void* stream);
+/* Single-token decode attention over a contiguous KV cache [B, S_max, Hk, D] with per-row lengths. */
+int dla_attn_decode(const void* q, const void* kcache, const void* vcache, void* o,
+                    const int32_t* lens, int B, int S_max, int Hq, int Hk, int D, float scale,
+                    void* stream);
+
+/* ---------------------------------------------------------------- sampling (K16) */
+/* Per-row temperature + top-p + multinomial on fp32/bf16 logits [B,V]; writes int64 token ids.
+ * scratch: dla_sampler_scratch_bytes(B, V). seed/offset: Philox-style counter RNG. */
+int dla_sample_top_p(const void* logits, int logits_fp32, int B, int V, int64_t ld, float temperature,
+                     float top_p, uint64_t seed, uint64_t offset, void* scratch, int64_t* out,
+                     void* stream);
+size_t dla_sampler_scratch_bytes(int B, int V);
+
+/* ---------------------------------------------------------------- peer-memory fused collectives */
+/* (a) reduce-scatter + cast/scale + grad-norm partial + sharded AdamW in one kernel: every rank
+ * reads the W peer copies of ITS shard of the bf16 gradient bucket over NVLink (peer_grads: device
+ * array of W device pointers to the full-size buckets), reduces in fp32, optionally accumulates
+ * sum(g^2) and applies AdamW to its fp32 shard, writing the updated bf16 shard into every peer's
+ * parameter buffer (peer_params, nullable => local only).  mode: 0 = reduce only into grad_out,
+ * 1 = reduce + sumsq, 2 = reduce + adamw.  R: NCCL reduce_scatter + clip + AdamW,
+ * R/src/training/train_dpo.py:118-120. */
+int dla_fused_rs_adamw(const void* const* peer_grads, void* const* peer_params, int world, int rank,
+                       int64_t shard_elems, int64_t shard_offset, float grad_scale,
+                       float* grad_out_fp32, float* sumsq_out, float* master, float* m, float* v,
+                       float lr, float beta1, float beta2, float eps, float weight_decay,
+                       float bias_c1, float bias_c2, const float* clip_coef_dev, int mode,
+                       void* stream);
+/* Signal-pad barrier across ranks (system-scope release/acquire flags in peer memory).
+ * pads: device array of W pointers to each rank's uint32 pad [W * channels]. */
+int dla_peer_barrier(uint32_t* const* pads, int world, int rank, int channel, uint32_t epoch,
+                     int timeout_ms, void* stream);
+/* (b) all-gather fused GEMM: C[M,N] = A[M,K] * Wfull[N,K]^T where Wfull's rows are sharded across
+ * ranks (rank r owns rows [r*N/W, (r+1)*N/W)); B tiles are TMA-loaded straight from the owning
+ * peer's memory (peer_maps built over peer pointers) into the tcgen05 pipeline. */
+int dla_ag_gemm_bf16(const void* A, const void* const* peer_B_host, void* C, int M, int N, int K,
+                     int64_t lda, int64_t ldb, int64_t ldc, int world, int c_fp32, int accumulate,
+                     void* stream);
+/* (c) cross-rank all-gather of per-sequence log-probs fused with the DPO loss: each rank writes its
+ * [4, B] block into every peer's gather buffer, barriers, then reduces loss / preference rate /
+ * margin over all W*B pairs and produces its local gradients. */
+int dla_fused_gather_dpo(float* const* peer_bufs, uint32_t* const* pads, int world, int rank,
+                         const float* pol_pos, const float* pol_neg, const float* ref_pos,
+                         const float* ref_neg, int B, float beta, float label_smoothing,
+                         uint32_t epoch, float* out, float* dpol_pos, float* dpol_neg, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DLA_B200_H_ */

@@ -1,0 +1,248 @@
+"""sm_100a kernel numerics vs plain PyTorch fp32 restatements."""
+import math
+
+import pytest
+import torch
+
+from dla_b200.ops import functional as F
+from dla_b200.ops import reference as R
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+BF16 = torch.bfloat16
+
+
+def _rand(*shape, scale=1.0, dtype=BF16):
+    return (torch.randn(*shape, device=DEV, dtype=torch.float32) * scale).to(dtype)
+
+
+def _rel(a, b, tol, what=""):
+    a, b = a.float(), b.float()
+    err = ((a - b).norm() / b.norm().clamp(min=1e-12)).item()
+    assert err < tol, f"{what}: relative Frobenius error {err:.4g} >= {tol}"
+
+
+def _close(a, b, rtol=2e-2, atol=2e-2, what=""):
+    a, b = a.float(), b.float()
+    err = (a - b).abs().max().item()
+    ref = b.abs().max().item()
+    assert torch.allclose(a, b, rtol=rtol, atol=atol), f"{what}: max err {err:.4g} (ref max {ref:.4g})"
+
+
+@pytest.mark.parametrize("M,H", [(64, 256), (333, 4096), (17, 8192)])
+def test_rmsnorm_fwd_bwd(native_lib, M, H):
+    torch.manual_seed(0)
+    x, d, w = _rand(M, H), _rand(M, H), _rand(H, scale=0.5) + 1
+    xr, dr, wr = (t.float().requires_grad_() for t in (x, d, w))
+    resid_ref = (xr + dr).to(BF16).float()
+    y_ref = R.rmsnorm(xr + dr, wr, 1e-5)
+    xg, dg, wg = (t.clone().requires_grad_() for t in (x, d, w))
+    resid, y = F.add_rmsnorm(xg, dg, wg, 1e-5)
+    _close(resid, resid_ref, what="resid")
+    _close(y, y_ref, what="y")
+    gy, gr = _rand(M, H), _rand(M, H)
+    (y_ref * gy.float()).sum().backward(retain_graph=True)
+    ((xr + dr) * gr.float()).sum().backward()
+    torch.autograd.backward([y, resid], [gy, gr])
+    _close(xg.grad, xr.grad, atol=6e-2, what="dx")
+    _close(dg.grad, dr.grad, atol=6e-2, what="ddelta")
+    _close(wg.grad, wr.grad, rtol=3e-2, atol=0.5, what="dw")
+
+
+@pytest.mark.parametrize("M,H", [(50, 768), (129, 2560)])
+def test_layernorm_fwd_bwd(native_lib, M, H):
+    torch.manual_seed(1)
+    x, w, b = _rand(M, H), _rand(H, scale=0.5) + 1, _rand(H, scale=0.1)
+    xr, wr, br = (t.float().requires_grad_() for t in (x, w, b))
+    y_ref = R.layernorm(xr, wr, br, 1e-5)
+    xg, wg, bg = (t.clone().requires_grad_() for t in (x, w, b))
+    y = F.layernorm(xg, wg, bg, 1e-5)
+    _close(y, y_ref, what="y")
+    g = _rand(M, H)
+    (y_ref * g.float()).sum().backward()
+    y.backward(g)
+    _close(xg.grad, xr.grad, atol=6e-2, what="dx")
+    _close(wg.grad, wr.grad, rtol=3e-2, atol=0.5, what="dw")
+    _close(bg.grad, br.grad, rtol=3e-2, atol=0.5, what="db")
+
+
+def test_rope_qkv(native_lib):
+    torch.manual_seed(2)
+    B, T, Hq, Hk, D = 2, 37, 8, 2, 128
+    M = B * T
+    qkv = _rand(M, (Hq + 2 * Hk) * D)
+    pos = torch.arange(T, device=DEV).repeat(B)
+    q, k, v = qkv.float().split([Hq * D, Hk * D, Hk * D], -1)
+    qr = R.rope(q.reshape(B, T, Hq, D), pos.reshape(B, T), 500000.0)
+    kr = R.rope(k.reshape(B, T, Hk, D), pos.reshape(B, T), 500000.0)
+    want = torch.cat([qr.reshape(M, -1), kr.reshape(M, -1), v], -1)
+    x = qkv.clone().requires_grad_()
+    out = F.rope_qkv(x * 1, pos, Hq, Hk, D, 500000.0, max_pos=64)
+    _close(out, want, what="rope fwd")
+    # rotation is orthogonal: backward of sum(out * g) is the inverse rotation of g
+    g = _rand(M, (Hq + 2 * Hk) * D)
+    out.backward(g)
+    gq, gk, gv = g.float().split([Hq * D, Hk * D, Hk * D], -1)
+    xq = qkv.float().requires_grad_()
+    q2, k2, v2 = xq.split([Hq * D, Hk * D, Hk * D], -1)
+    o2 = torch.cat([R.rope(q2.reshape(B, T, Hq, D), pos.reshape(B, T), 500000.0).reshape(M, -1),
+                    R.rope(k2.reshape(B, T, Hk, D), pos.reshape(B, T), 500000.0).reshape(M, -1), v2], -1)
+    (o2 * g.float()).sum().backward()
+    _close(x.grad, xq.grad, what="rope bwd")
+
+
+def test_swiglu_gelu(native_lib):
+    torch.manual_seed(3)
+    gu = _rand(77, 2 * 1024)
+    a = gu.clone().requires_grad_()
+    b = gu.float().requires_grad_()
+    y, yr = F.swiglu(a), R.swiglu(b)
+    _close(y, yr, what="swiglu")
+    g = _rand(77, 1024)
+    y.backward(g)
+    (yr * g.float()).sum().backward()
+    _close(a.grad, b.grad, atol=4e-2, what="swiglu bwd")
+    x, bias = _rand(33, 3072), _rand(3072, scale=0.1)
+    xa, ba = x.clone().requires_grad_(), bias.clone().requires_grad_()
+    xb, bb = x.float().requires_grad_(), bias.float().requires_grad_()
+    y, yr = F.gelu_bias(xa, ba), R.gelu_tanh(xb + bb)
+    _close(y, yr, what="gelu")
+    g = _rand(33, 3072)
+    y.backward(g)
+    (yr * g.float()).sum().backward()
+    _close(xa.grad, xb.grad, atol=4e-2, what="gelu dx")
+    _close(ba.grad, bb.grad, rtol=3e-2, atol=0.3, what="gelu db")
+
+
+def test_embedding(native_lib):
+    torch.manual_seed(4)
+    V, H, B, T = 1000, 256, 3, 40
+    table, pos = _rand(V, H), _rand(T, H)
+    ids = torch.randint(0, V, (B, T), device=DEV)
+    ta, pa = table.clone().requires_grad_(), pos.clone().requires_grad_()
+    tb, pb = table.float().requires_grad_(), pos.float().requires_grad_()
+    y = F.embedding(ids, ta, pa)
+    yr = torch.nn.functional.embedding(ids, tb) + pb[:T]
+    _close(y, yr, what="embedding")
+    g = _rand(B, T, H)
+    y.backward(g)
+    (yr * g.float()).sum().backward()
+    _close(ta.grad, tb.grad, atol=6e-2, what="dtable")
+    _close(pa.grad, pb.grad, atol=6e-2, what="dpos")
+
+
+GEMM_SHAPES = [(128, 256, 64), (128, 256, 256), (256, 512, 4096), (300, 520, 1032), (4096, 4096, 4096),
+               (1000, 14336, 4096), (8, 128256, 64)]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_nt(native_lib, M, N, K):
+    torch.manual_seed(5)
+    a, b = _rand(M, K), _rand(N, K)
+    c = F.gemm(a, b)
+    ref = a.float() @ b.float().t()
+    _close(c, ref, rtol=2e-2, atol=0.02 * math.sqrt(K), what=f"gemm NT {M}x{N}x{K}")
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 1024), (520, 1032, 304), (4096, 4096, 1024)])
+def test_gemm_layout_variants(native_lib, M, N, K):
+    torch.manual_seed(6)
+    a, b = _rand(M, K), _rand(N, K)
+    ref = a.float() @ b.float().t()
+    tol = dict(rtol=2e-2, atol=0.02 * math.sqrt(K))
+    _close(F.gemm(a, b.t().contiguous(), b_mn=True), ref, what="NN (B mn-major)", **tol)
+    _close(F.gemm(a.t().contiguous(), b, a_mn=True), ref, what="TN (A mn-major)", **tol)
+    _close(F.gemm(a.t().contiguous(), b.t().contiguous(), a_mn=True, b_mn=True), ref, what="TT", **tol)
+    out = torch.ones(M, N, device=DEV, dtype=torch.float32)
+    F.gemm(a, b, out=out, accumulate=True)
+    _close(out, ref + 1, what="fp32 accumulate", **tol)
+    outb = torch.ones(M, N, device=DEV, dtype=BF16)
+    F.gemm(a, b, out=outb, accumulate=True)
+    _close(outb, ref + 1, what="bf16 accumulate", rtol=2e-2, atol=0.03 * math.sqrt(K))
+
+
+def test_linear_autograd(native_lib):
+    torch.manual_seed(7)
+    x, w, b = _rand(4, 64, 512, scale=0.5), _rand(1024, 512, scale=0.05), _rand(1024, scale=0.1)
+    xa, wa, ba = (t.clone().requires_grad_() for t in (x, w, b))
+    xb, wb, bb = (t.float().requires_grad_() for t in (x, w, b))
+    y, yr = F.linear(xa, wa, ba), torch.nn.functional.linear(xb, wb, bb)
+    _close(y, yr, what="linear fwd")
+    g = _rand(4, 64, 1024)
+    y.backward(g)
+    (yr * g.float()).sum().backward()
+    _close(xa.grad, xb.grad, atol=5e-2, what="dx")
+    _close(wa.grad, wb.grad, rtol=3e-2, atol=0.5, what="dw")
+    _close(ba.grad, bb.grad, rtol=3e-2, atol=0.5, what="db")
+
+
+@pytest.mark.parametrize("M,V,K", [(128, 512, 256), (300, 1000, 512), (520, 128256, 256)])
+def test_linear_logprob(native_lib, M, V, K):
+    torch.manual_seed(8)
+    h, w = _rand(M, K), _rand(V, K, scale=0.05)
+    labels = torch.randint(0, V, (M,), device=DEV)
+    labels[::7] = -100
+    ha, wa = h.clone().requires_grad_(), w.clone().requires_grad_()
+    hb, wb = h.float().requires_grad_(), w.float().requires_grad_()
+    lp, lse = F.linear_logprob(ha, wa, labels)
+    lpr, lser = R.token_logprobs(hb, wb, labels)
+    _close(lp, lpr, atol=3e-2, what="logp")
+    _close(lse, lser, atol=3e-2, what="lse")
+    if V % 8 == 0:
+        g = torch.randn(M, device=DEV)
+        lp.backward(g)
+        (lpr * g).sum().backward()
+        _rel(ha.grad, hb.grad, 2e-2, what="dh")
+        _rel(wa.grad, wb.grad, 2e-2, what="dw")
+
+
+def test_adamw_and_norm(native_lib):
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(9)
+    n = 100_003 * 8
+    master = torch.randn(n, device=DEV)
+    m, v = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    grad = _rand(n, scale=0.1)
+    ref_p = master.clone().requires_grad_()
+    opt = torch.optim.AdamW([ref_p], lr=1e-2, betas=(0.9, 0.95), eps=1e-8, weight_decay=0.01)
+    param = torch.empty(n, device=DEV, dtype=BF16)
+    scratch = torch.empty(N.sumsq_blocks(), device=DEV)
+    ss = torch.zeros(1, device=DEV)
+    coef, norm = torch.empty(1, device=DEV), torch.empty(1, device=DEV)
+    for step in (1, 2, 3):
+        ref_p.grad = grad.float().clone()
+        total = torch.nn.utils.clip_grad_norm_([ref_p], 1.0)
+        opt.step()
+        N.call("dla_sumsq", N.ptr(grad), n, 0, N.ptr(scratch), N.ptr(ss), 0, N.stream_ptr())
+        N.call("dla_clip_coef", N.ptr(ss), 1.0, N.ptr(coef), N.ptr(norm), N.stream_ptr())
+        assert abs(norm.item() - total.item()) / total.item() < 1e-3
+        N.call("dla_adamw", N.ptr(master), N.ptr(m), N.ptr(v), N.ptr(grad), N.ptr(param), n, 1e-2, 0.9, 0.95, 1e-8,
+               0.01, 1 - 0.9 ** step, 1 - 0.95 ** step, N.ptr(coef), 1.0, 0, N.stream_ptr())
+    _close(master, ref_p.detach(), rtol=1e-4, atol=1e-5, what="adamw master")
+    _close(param, ref_p.detach(), rtol=1e-2, atol=1e-2, what="adamw bf16 param")
+
+
+def test_losses(native_lib):
+    torch.manual_seed(10)
+    B = 37
+    pp, pn, rp, rn = (torch.randn(B, device=DEV) for _ in range(4))
+    a, b = pp.clone().requires_grad_(), pn.clone().requires_grad_()
+    loss, stats = F.dpo_loss(a, b, rp, rn, 0.1, 0.05)
+    ar, br = pp.clone().requires_grad_(), pn.clone().requires_grad_()
+    ref = R.dpo_loss(ar, br, rp, rn, 0.1, 0.05)
+    _close(loss, ref, atol=1e-5, rtol=1e-5, what="dpo loss")
+    loss.backward()
+    ref.backward()
+    _close(a.grad, ar.grad, atol=1e-6, rtol=1e-4, what="dpo dpos")
+    _close(b.grad, br.grad, atol=1e-6, rtol=1e-4, what="dpo dneg")
+    assert abs(stats[0].item() - (pp > pn).float().mean().item()) < 1e-6
+    c, r = torch.randn(B, device=DEV, requires_grad=True), torch.randn(B, device=DEV, requires_grad=True)
+    l2, acc = F.pairwise_loss(c, r)
+    _close(l2, R.pairwise_loss(c.detach(), r.detach()), atol=1e-5, what="pairwise")
+    tok = torch.randn(5, 33, device=DEV, requires_grad=True)
+    mask = (torch.rand(5, 33, device=DEV) > 0.3).long()
+    s = F.sequence_logprob(tok, mask)
+    _close(s, R.sequence_mean_logprob(tok.detach(), mask), atol=1e-5, what="seq mean")
+    s.sum().backward()
+    _close(tok.grad, mask.float() / mask.sum(1, keepdim=True).clamp(min=1), atol=1e-6, what="seq mean bwd")
