@@ -81,6 +81,15 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
       : "memory");
 }
 
+// 4D tile load (coordinates innermost first)
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05
 template <int kCtas>
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_holder, uint32_t ncols) {
@@ -208,5 +217,8 @@ __device__ __forceinline__ void cluster_sync() {
 // (box0, box1), SWIZZLE_128B (box0 * 2 bytes must be <= 128).
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, uint64_t ld_elems,
                       uint32_t box0, uint32_t box1);
+// Rank-4 bf16 map: dims[0] contiguous; strides_elems[i] is the pitch of dims[i+1] in elements.
+int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_elems[3],
+                      const uint32_t box[4]);
 
 }  // namespace dla

@@ -434,10 +434,17 @@ class _Attention(Function):
         B, T, Hq, D = q.shape
         Hk = k.shape[2]
         do = _c(do)
-        # gradients are produced in one packed [B, T, Hq + 2 Hk, D] buffer so that, when q/k/v were
-        # views of one fused projection, autograd's view backward concatenates without extra copies
-        dqkv = torch.empty(B, T, Hq + 2 * Hk, D, dtype=q.dtype, device=q.device)
-        dq, dk, dv = dqkv[:, :, :Hq], dqkv[:, :, Hq:Hq + Hk], dqkv[:, :, Hq + Hk:]
+        # dq/dk/dv take the strides of q/k/v.  When q, k, v are views of one fused projection the three
+        # gradients are views of one packed [B, T, Hq + 2 Hk, D] buffer, so autograd's view backward
+        # reassembles d(qkv) without extra copies.
+        packed = (q.stride() == k.stride() == v.stride() and q.stride(2) == D and q.stride(1) == (Hq + 2 * Hk) * D
+                  and k.data_ptr() - q.data_ptr() == Hq * D * 2 and v.data_ptr() - k.data_ptr() == Hk * D * 2)
+        if packed:
+            dqkv = torch.empty(B, T, Hq + 2 * Hk, D, dtype=q.dtype, device=q.device)
+            dq, dk, dv = dqkv[:, :, :Hq], dqkv[:, :, Hq:Hq + Hk], dqkv[:, :, Hq + Hk:]
+        else:
+            q, k, v = _c(q), _c(k), _c(v)
+            dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
         dq_acc = torch.empty(B, T, Hq, D, dtype=torch.float32, device=q.device)
         delta = torch.empty(B, Hq, T, dtype=torch.float32, device=q.device)
         assert do.stride(2) == o.stride(2) and do.stride(1) == o.stride(1) and do.stride(0) == o.stride(0)

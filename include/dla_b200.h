@@ -152,7 +152,8 @@ int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
                  int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
                  int64_t o_sb, int64_t o_st, int64_t o_sh,
                  const int32_t* seqlens, float scale, int causal, void* stream);
-/* Backward. dq_acc: fp32 scratch [B,T,Hq,D] (zeroed inside); delta: fp32 scratch [B,Hq,T]. */
+/* Backward. dq_acc: fp32 scratch [B,T,Hq,D] (zeroed inside); delta: fp32 scratch [B,Hq,T].
+ * dq must have q's strides, dk/dv must have k/v's strides; dout must have o's strides. */
 int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
                  const float* lse, void* dq, void* dk, void* dv, float* dq_acc, float* delta,
                  int B, int T, int Hq, int Hk, int D,

@@ -246,3 +246,64 @@ def test_losses(native_lib):
     _close(s, R.sequence_mean_logprob(tok.detach(), mask), atol=1e-5, what="seq mean")
     s.sum().backward()
     _close(tok.grad, mask.float() / mask.sum(1, keepdim=True).clamp(min=1), atol=1e-6, what="seq mean bwd")
+
+
+ATTN_CASES = [  # B, T, Hq, Hk, D, ragged
+    (1, 128, 1, 1, 128, False), (2, 256, 4, 2, 128, False), (2, 384, 8, 2, 128, True),
+    (1, 200, 2, 1, 128, True), (2, 256, 4, 4, 64, True), (1, 1024, 8, 2, 128, False),
+]
+
+
+@pytest.mark.parametrize("B,T,Hq,Hk,D,ragged", ATTN_CASES)
+def test_attention_fwd_bwd(native_lib, B, T, Hq, Hk, D, ragged):
+    torch.manual_seed(11)
+    qkv = _rand(B, T, Hq + 2 * Hk, D)
+    seqlens = None
+    if ragged:
+        seqlens = torch.randint(max(1, T // 3), T + 1, (B,), device=DEV, dtype=torch.int32)
+        seqlens[0] = T - 5 if T > 8 else T
+    x = qkv.clone().requires_grad_()
+    q, k, v = x[:, :, :Hq], x[:, :, Hq:Hq + Hk], x[:, :, Hq + Hk:]
+    o = F.attention(q, k, v, seqlens=seqlens, causal=True)
+    xr = qkv.float().requires_grad_()
+    qr, kr, vr = xr[:, :, :Hq], xr[:, :, Hq:Hq + Hk], xr[:, :, Hq + Hk:]
+    oref = R.attention(qr, kr, vr, causal=True, seqlens=seqlens)
+    _close(o, oref, rtol=2e-2, atol=2e-2, what="attn fwd")
+    g = _rand(B, T, Hq, D)
+    if seqlens is not None:  # padded query rows carry no gradient in training
+        g = g * (torch.arange(T, device=DEV)[None, :] < seqlens[:, None])[:, :, None, None]
+    o.backward(g)
+    (oref * g.float()).sum().backward()
+    _rel(x.grad[:, :, :Hq], xr.grad[:, :, :Hq], 3e-2, what="dq")
+    _rel(x.grad[:, :, Hq:Hq + Hk], xr.grad[:, :, Hq:Hq + Hk], 3e-2, what="dk")
+    _rel(x.grad[:, :, Hq + Hk:], xr.grad[:, :, Hq + Hk:], 3e-2, what="dv")
+
+
+def test_attention_separate_tensors(native_lib):
+    torch.manual_seed(12)
+    B, T, Hq, Hk, D = 2, 256, 4, 2, 128
+    q, k, v = _rand(B, T, Hq, D), _rand(B, T, Hk, D), _rand(B, T, Hk, D)
+    qa, ka, va = (t.clone().requires_grad_() for t in (q, k, v))
+    qb, kb, vb = (t.float().requires_grad_() for t in (q, k, v))
+    o, oref = F.attention(qa, ka, va), R.attention(qb, kb, vb)
+    _close(o, oref, what="attn fwd (separate)")
+    g = _rand(B, T, Hq, D)
+    o.backward(g)
+    (oref * g.float()).sum().backward()
+    _rel(qa.grad, qb.grad, 3e-2, what="dq")
+    _rel(ka.grad, kb.grad, 3e-2, what="dk")
+    _rel(va.grad, vb.grad, 3e-2, what="dv")
+
+
+def test_attention_decode(native_lib):
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(13)
+    B, S, Hq, Hk, D = 3, 300, 8, 2, 128
+    q, kc, vc = _rand(B, Hq, D), _rand(B, S, Hk, D), _rand(B, S, Hk, D)
+    lens = torch.tensor([300, 17, 128], device=DEV, dtype=torch.int32)
+    o = torch.empty(B, Hq, D, device=DEV, dtype=BF16)
+    N.call("dla_attn_decode", N.ptr(q), N.ptr(kc), N.ptr(vc), N.ptr(o), N.ptr(lens), B, S, Hq, Hk, D, 1 / math.sqrt(D),
+           N.stream_ptr())
+    ref = R.attention(q[:, None], kc, vc, causal=False, seqlens=lens)[:, 0]
+    _close(o, ref, what="decode attention")
