@@ -1,0 +1,125 @@
+"""Reference arm of bench.py: the reference's own DPO step on stock PyTorch / transformers.
+
+What runs: ``compute_logprobs`` and ``dpo_loss`` imported UNMODIFIED from the reference tree
+(``baseline/_ref/distributed-llm-alignment/src/training/train_dpo.py``, falling back to ``/root/reference``),
+driven in the order of its hot loop (``R/src/training/train_dpo.py:110-121``: four log-prob passes,
+loss, backward, clip_grad_norm_, AdamW step, zero_grad) on ``transformers.LlamaForCausalLM`` (cuBLAS GEMMs,
+PyTorch SDPA, ATen log_softmax) with torch DDP / FSDP2 + NCCL.  None of dla_b200's models, kernels or
+engine is on this path.
+
+Why not ``pip install`` + the reference's ``main()``: the tree has no setup.py/pyproject (pip refuses it,
+see DESIGN.md) and its trainers import ``accelerate`` — not installed, not installable offline — and
+load weights with ``from_pretrained(..., device_map="auto")`` from the hub.  So a stand-in ``accelerate``
+module is registered only to let the file import; the model is random-init from the named config, and
+the distributed wrapping accelerate would do (``prepare``) is done with the torch primitives it delegates to.
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+from pathlib import Path
+from typing import Any, Dict, Tuple
+
+import torch
+import torch.distributed as dist
+
+HERE = Path(__file__).resolve().parent
+CANDIDATES = [HERE / "_ref" / "distributed-llm-alignment", Path("/root/reference/distributed-llm-alignment")]
+
+
+def locate() -> Path | None:
+    for c in CANDIDATES:
+        if (c / "src" / "training" / "train_dpo.py").exists():
+            return c
+    return None
+
+
+def import_reference_fns():
+    root = locate()
+    if root is None:
+        raise FileNotFoundError("reference tree not found under baseline/_ref or /root/reference")
+    if "accelerate" not in sys.modules:
+        try:
+            import accelerate  # noqa: F401
+        except Exception:
+            acc = types.ModuleType("accelerate")
+            for n in ("Accelerator", "DeepSpeedPlugin", "FullyShardedDataParallelPlugin"):
+                setattr(acc, n, type(n, (), {}))
+            util = types.ModuleType("accelerate.utils")
+            util.DistributedDataParallelKwargs = type("DistributedDataParallelKwargs", (), {"__init__": lambda self, **k: None})
+            acc.utils = util
+            sys.modules["accelerate"], sys.modules["accelerate.utils"] = acc, util
+    sys.path.insert(0, str(root))
+    try:
+        from src.training.train_dpo import compute_logprobs, dpo_loss  # type: ignore
+    finally:
+        sys.path.pop(0)
+    return compute_logprobs, dpo_loss, root
+
+
+def llama_hf_config(name: str):
+    from transformers import LlamaConfig
+
+    presets = {
+        "llama3-8b": dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=32,
+                          num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=8192,
+                          rope_theta=500000.0, rms_norm_eps=1e-5),
+        "llama-1b": dict(vocab_size=32000, hidden_size=2048, intermediate_size=5632, num_hidden_layers=16,
+                         num_attention_heads=16, num_key_value_heads=4, max_position_embeddings=4096,
+                         rope_theta=500000.0, rms_norm_eps=1e-5),
+        "tiny-llama": dict(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                           num_attention_heads=2, num_key_value_heads=1, max_position_embeddings=512,
+                           rope_theta=10000.0, rms_norm_eps=1e-5),
+    }
+    cfg = LlamaConfig(**presets[name], tie_word_embeddings=False, attn_implementation="sdpa")
+    cfg.use_cache = False
+    return cfg
+
+
+class ReferenceDPO:
+    """Policy + frozen reference as the reference builds them (policy with gradient checkpointing,
+    reference without, AdamW(lr, weight_decay=0.01), max_grad_norm 1.0) wrapped for N ranks."""
+
+    def __init__(self, model_name: str, device: torch.device, world: int, lr: float = 1e-6, beta: float = 0.1,
+                 sharded: bool = True) -> None:
+        from transformers import LlamaForCausalLM
+
+        self.compute_logprobs, self.dpo_loss, self.root = import_reference_fns()
+        cfg = llama_hf_config(model_name)
+        self.device, self.world, self.beta = device, world, beta
+        torch.manual_seed(0)
+        with torch.device(device):
+            policy = LlamaForCausalLM(cfg).to(torch.bfloat16)
+            ref = LlamaForCausalLM(cfg).to(torch.bfloat16)
+        policy.gradient_checkpointing_enable()
+        policy.train()      # HF only checkpoints in train mode; Llama has no dropout so the math is unchanged
+        ref.eval()
+        for p in ref.parameters():
+            p.requires_grad = False
+        if world > 1:
+            if sharded:
+                from torch.distributed.fsdp import fully_shard
+
+                for m in (policy, ref):
+                    for layer in m.model.layers:
+                        fully_shard(layer)
+                    fully_shard(m)
+            else:
+                policy = torch.nn.parallel.DistributedDataParallel(policy, device_ids=[device.index], find_unused_parameters=False)
+        self.policy, self.ref = policy, ref
+        self.opt = torch.optim.AdamW(policy.parameters(), lr=lr, weight_decay=0.01)
+
+    def step(self, batch: Dict[str, Dict[str, torch.Tensor]]) -> torch.Tensor:
+        ch, rj = batch["chosen"], batch["rejected"]
+        with torch.autocast("cuda", dtype=torch.bfloat16):      # accelerate mixed_precision=bf16 wraps forward
+            pol_pos = self.compute_logprobs(self.policy, ch["input_ids"], ch["attention_mask"])
+            pol_neg = self.compute_logprobs(self.policy, rj["input_ids"], rj["attention_mask"])
+            ref_pos = self.compute_logprobs(self.ref, ch["input_ids"], ch["attention_mask"])
+            ref_neg = self.compute_logprobs(self.ref, rj["input_ids"], rj["attention_mask"])
+            loss = self.dpo_loss(pol_pos, pol_neg, ref_pos, ref_neg, self.beta)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(self.policy.parameters(), 1.0)
+        self.opt.step()
+        self.opt.zero_grad()
+        return loss.detach()

@@ -362,9 +362,9 @@ logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, co
                     const float* __restrict__ grow, int Mc, int V, int64_t ld) {
   const int m = blockIdx.y;
   if (m >= Mc) return;
-  const float g = grow[m];
-  const float l = lse[m];
   const int64_t lab = labels[m];
+  const float g = lab >= 0 ? grow[m] : 0.f;   // ignored positions (label < 0) carry no gradient
+  const float l = lse[m];
   bf16* row = logits + (int64_t)m * ld;
   const int nvec = V >> 3;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += gridDim.x * blockDim.x) {

@@ -1,0 +1,94 @@
+"""Model construction from a path / preset under a hardware plan.
+
+Parity: ``load_causal_lm`` returns a ``ModelBundle(model, tokenizer)`` with ``pad_token := eos_token`` when
+missing, bf16 on CUDA / fp32 on CPU and optional gradient checkpointing
+(``R/src/models/base_model.py:17-42``); ``build_reward_model`` returns ``(model, tokenizer)``
+(``R/src/models/reward_model.py:20-35``); ``count_trainable_params`` / ``freeze_except_lora`` mirror
+``R/src/models/base_model.py:45-59``.  Differences: models are built straight into the (sharded) engine
+instead of ``device_map="auto"`` + re-wrap (defect D1), and weights are random-init unless the directory
+holds safetensors (no hub access).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from pathlib import Path
+from typing import Any, Dict, List, Optional, Tuple
+
+import torch
+
+from dla_b200.config import HardwarePlan
+from dla_b200.data.tokenizer import load_tokenizer
+from dla_b200.models.config import ModelConfig, resolve_model_config
+from dla_b200.models.io import has_pretrained_weights
+from dla_b200.models.reward import RewardModel, reward_units, value_head_unit
+from dla_b200.models.transformer import CausalLM, build_units
+from dla_b200.parallel.engine import Engine
+from dla_b200.parallel.pg import DistContext
+
+
+@dataclass
+class ModelBundle:
+    model: Any
+    tokenizer: Any
+    engine: Optional[Engine] = None
+    config: Optional[ModelConfig] = None
+
+
+def _engine(cfg: ModelConfig, units, ctx: DistContext, plan: Optional[HardwarePlan], trainable: bool,
+            checkpoint: bool, seed: int, name: str, dtype: Optional[torch.dtype]) -> Engine:
+    plan = plan or HardwarePlan()
+    state_dtype = torch.bfloat16 if plan.optimizer_state_dtype == "bf16" else torch.float32
+    return Engine(cfg, units, ctx, sharding=plan.sharding, trainable=trainable, checkpoint=checkpoint, dtype=dtype,
+                  seed=seed, resident=plan.resident_params, state_dtype=state_dtype, comm=plan.comm, name=name)
+
+
+def load_causal_lm(model_name_or_path: str, ctx: DistContext, plan: Optional[HardwarePlan] = None,
+                   gradient_checkpointing: bool = True, use_flash_attention: bool = False,
+                   torch_dtype: Optional[torch.dtype] = None, trainable: bool = True, seed: int = 0,
+                   name: str = "policy", extra_units: Optional[List] = None) -> ModelBundle:
+    """``use_flash_attention`` is accepted for config compatibility; attention is always the fused
+    flash kernel here (in the reference the flag only sets ``use_cache=False``,
+    ``R/src/models/base_model.py:39-40``)."""
+    cfg = resolve_model_config(model_name_or_path)
+    tokenizer = load_tokenizer(model_name_or_path, cfg.vocab_size)
+    if getattr(tokenizer, "pad_token", None) is None:
+        tokenizer.pad_token = tokenizer.eos_token
+    units = build_units(cfg) + list(extra_units or [])
+    eng = _engine(cfg, units, ctx, plan, trainable, gradient_checkpointing, seed, name, torch_dtype)
+    if has_pretrained_weights(model_name_or_path):
+        from dla_b200.ckpt import load_model_dir
+
+        load_model_dir(eng, model_name_or_path)
+    return ModelBundle(model=CausalLM(cfg, eng), tokenizer=tokenizer, engine=eng, config=cfg)
+
+
+def build_reward_model(base_model_name_or_path: str, ctx: DistContext, plan: Optional[HardwarePlan] = None,
+                       pooling: str = "last_token", dropout: float = 0.1, trainable: bool = True,
+                       gradient_checkpointing: bool = True, seed: int = 0, name: str = "reward",
+                       checkpoint_path: Optional[str] = None) -> Tuple[RewardModel, Any]:
+    cfg = resolve_model_config(base_model_name_or_path)
+    tokenizer = load_tokenizer(base_model_name_or_path, cfg.vocab_size)
+    if getattr(tokenizer, "pad_token", None) is None:
+        tokenizer.pad_token = tokenizer.eos_token
+    eng = _engine(cfg, reward_units(cfg), ctx, plan, trainable, gradient_checkpointing, seed, name, None)
+    from dla_b200.ckpt import load_model_dir
+
+    for src in (base_model_name_or_path, checkpoint_path):
+        if src and has_pretrained_weights(src):
+            load_model_dir(eng, src)     # strict=False semantics like R/src/training/train_rlhf.py:84
+    model = RewardModel(cfg, eng, pooling=pooling, dropout=dropout)  # type: ignore[arg-type]
+    return model, tokenizer
+
+
+def freeze_except_lora(engine: Engine, lora_layers: Optional[str] = None) -> None:
+    """Substring-based freeze (``R/src/models/base_model.py:45-49``; dead code there).  Units with no
+    matching parameter stop producing gradients; matching is per parameter name."""
+    engine.frozen_filter = lora_layers  # consulted by optimizer_step via Engine.param_mask
+
+
+def count_trainable_params(engine: Engine) -> Dict[str, Any]:
+    """total / trainable / ratio (``R/src/models/base_model.py:52-59``)."""
+    total = engine.num_params()
+    trainable = total if engine.trainable else 0
+    return {"total_params": total, "trainable_params": trainable,
+            "trainable_ratio": trainable / total if total else 0.0}

@@ -369,13 +369,13 @@ class CausalLM:
         ``R/src/training/train_dpo.py:33-36``).  ``labels`` (default ``input_ids``) may carry -100."""
         h = self.hidden(input_ids, attention_mask, **kw)
         B, T, H = h.shape
-        tgt = (labels if labels is not None else input_ids)[:, 1:]
-        hs = h[:, :-1].reshape(B * (T - 1), H)
+        src = labels if labels is not None else input_ids
+        # all T positions go through the fused head (row count stays a multiple of 8 for the TMA path);
+        # the last position has no target and is marked ignored
+        tgt = torch.cat([src[:, 1:], torch.full_like(src[:, :1], -100)], dim=1)
         w, unit = self._lm_head_weight()
-        logp, _ = F.linear_logprob(hs, w, tgt.reshape(-1))
-        if torch.is_grad_enabled() and self.p.trainable:
-            _register_head_done(logp, self.p, unit)
-        return logp.view(B, T - 1)
+        logp, _ = F.linear_logprob(h.reshape(B * T, H), w, tgt.reshape(-1))
+        return logp.view(B, T)[:, :-1]
 
     def logits(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
                last_only: bool = False, **kw) -> torch.Tensor:

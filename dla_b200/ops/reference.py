@@ -79,8 +79,8 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, causal: bool = 
     p = torch.softmax(s, dim=-1)
     p = torch.where(mask.any(-1, keepdim=True), p, torch.zeros_like(p))
     o = torch.matmul(p, vf).permute(0, 2, 1, 3)
-    if seqlens is not None:
-        o = o * (torch.arange(T, device=q.device)[None, :] < seqlens[:, None] + (T - S))[:, :, None, None]
+    if seqlens is not None and T == S:
+        o = o * (torch.arange(T, device=q.device)[None, :] < seqlens[:, None])[:, :, None, None]
     return o.to(q.dtype)
 
 

@@ -1,0 +1,385 @@
+"""Parameter engine: replicated (DDP) and sharded (ZeRO-1/2/3 = FSDP FULL_SHARD) execution of a
+unit-structured model, with the sharded AdamW, gradient accumulation and global-norm clipping.
+
+What it replaces in the reference (all delegated there to accelerate / DeepSpeed / FSDP):
+  * ``accelerator.prepare(model, optimizer)`` — DDP wrap, FSDP shard or ``deepspeed.initialize``
+    (``R/src/training/train_dpo.py:79-82``; selected by ``R/src/training/utils.py:55-75``)
+  * ``accelerator.backward`` — bucketed grad all-reduce / per-unit reduce-scatter
+  * parameter all-gather before each unit's forward and backward
+  * ``accelerator.clip_grad_norm_`` + ``optimizer.step`` + ``zero_grad``
+  * ``accelerator.accumulate`` — collectives and the update only on accumulation boundaries
+
+B200-first choices: one flat bf16 buffer per unit (a decoder layer = 436 MB for Llama-3-8B) is the
+communication granule; with 180 GB of HBM the gathered bf16 parameters of an 8B model stay RESIDENT
+(16 GB) so only gradients (reduce-scatter) and updated shards (all-gather) cross NVLink once per
+optimizer step; models that do not fit (70B) stream units with one-unit-ahead prefetch.  fp32 master
+weights and Adam moments exist only for the rank's shard.  On CUDA the update runs the fused
+``dla_adamw`` kernel with the clip coefficient read from device memory (no host sync); with
+``comm="fused"`` the reduce-scatter itself happens inside the kernel over NVLink peer memory
+(:mod:`dla_b200.parallel.fused`).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from dla_b200.models.config import ModelConfig
+from dla_b200.models.transformer import (ParamProvider, UnitSpec, Weights, collect_autograd_grads, init_unit_,
+                                         unit_views)
+from dla_b200.ops import native as N
+from dla_b200.ops import reference as R
+from dla_b200.parallel.pg import DistContext
+
+SHARDED = ("zero1", "zero2", "zero3")
+
+
+@dataclass
+class AdamWConfig:
+    lr: float = 1e-5
+    betas: tuple = (0.9, 0.999)
+    eps: float = 1e-8
+    weight_decay: float = 0.0
+    max_grad_norm: float = 1.0
+
+
+class Engine(ParamProvider):
+    def __init__(self, cfg: ModelConfig, units: Sequence[UnitSpec], ctx: DistContext, sharding: str = "ddp",
+                 trainable: bool = True, checkpoint: bool = True, dtype: Optional[torch.dtype] = None, seed: int = 0,
+                 init: bool = True, resident: Optional[bool] = None, grad_dtype: Optional[torch.dtype] = None,
+                 state_dtype: torch.dtype = torch.float32, comm: str = "auto", name: str = "model",
+                 hbm_budget_bytes: Optional[int] = None) -> None:
+        self.cfg, self.units, self.ctx, self.name = cfg, list(units), ctx, name
+        self.sharding = sharding if ctx.world_size > 1 else "ddp"
+        self.trainable, self.checkpoint = trainable, checkpoint
+        self.device = ctx.device
+        self.dtype = dtype or (torch.bfloat16 if self.device.type == "cuda" else torch.float32)
+        self.grad_dtype = grad_dtype or self.dtype
+        self.state_dtype = state_dtype
+        self.W = ctx.world_size if self.sharding in SHARDED else 1     # shard group size
+        self.r = ctx.rank if self.W > 1 else 0
+        self.comm = comm
+        self._by_name = {u.name: u for u in self.units}
+        self._order = [u.name for u in self.units]
+        self.P = {u.name: u.padded_numel(8 * self.W) for u in self.units}
+        self.S = {k: v // self.W for k, v in self.P.items()}
+        total = sum(self.P.values())
+        if resident is None:
+            # keep gathered params (+ full grad buckets when trainable) resident if they fit comfortably
+            need = total * _bytes(self.dtype) * (2 if trainable else 1)
+            budget = hbm_budget_bytes if hbm_budget_bytes is not None else _default_budget(self.device)
+            resident = self.sharding != "zero3" or need <= budget
+        self.resident = bool(resident) or self.W == 1
+        self.full: Dict[str, Optional[torch.Tensor]] = {}
+        self.shard: Dict[str, torch.Tensor] = {}
+        self.gradbuf: Dict[str, Optional[torch.Tensor]] = {}
+        self.gshard: Dict[str, torch.Tensor] = {}
+        self.master: Dict[str, torch.Tensor] = {}
+        self.m: Dict[str, torch.Tensor] = {}
+        self.v: Dict[str, torch.Tensor] = {}
+        self._views: Dict[str, Weights] = {}
+        self._gather_work: Dict[str, Any] = {}
+        self._reduce_work: List[Any] = []
+        self._passes_expected = 1
+        self._passes_seen: Dict[str, int] = {}
+        self.sync_grads = True          # False on non-boundary accumulation micro-steps (``no_sync``)
+        self.step_count = 0
+        self._sumsq = None
+        self._coef = None
+        self.last_grad_norm: Optional[torch.Tensor] = None
+        self.stats = {"allgather_bytes": 0, "reduce_bytes": 0}
+        self._build(seed, init)
+
+    # ------------------------------------------------------------------ construction
+    def _build(self, seed: int, init: bool) -> None:
+        for ui, u in enumerate(self.units):
+            P, S = self.P[u.name], self.S[u.name]
+            full = torch.zeros(P, dtype=self.dtype, device=self.device)
+            if init:
+                gen = torch.Generator(device=self.device).manual_seed(seed * 1000003 + ui)
+                init_unit_(full, u, self.cfg, gen)
+            if self.W > 1:
+                self.shard[u.name] = full[self.r * S:(self.r + 1) * S].clone()
+                self.full[u.name] = full if self.resident else None
+            else:
+                self.shard[u.name] = full            # the rank owns the whole unit
+                self.full[u.name] = full
+            if self.trainable:
+                self.gradbuf[u.name] = torch.zeros(P, dtype=self.grad_dtype, device=self.device) if self.resident else None
+                if self.W > 1 and not self.resident:
+                    self.gshard[u.name] = torch.zeros(S, dtype=torch.float32, device=self.device)
+            del full
+        if self.trainable:
+            self._init_optimizer_state()
+
+    def _init_optimizer_state(self) -> None:
+        for u in self.units:
+            sh = self.shard[u.name]
+            self.master[u.name] = sh.float().clone()
+            self.m[u.name] = torch.zeros(sh.numel(), dtype=self.state_dtype, device=self.device)
+            self.v[u.name] = torch.zeros(sh.numel(), dtype=self.state_dtype, device=self.device)
+        if self.device.type == "cuda":
+            self._sumsq = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self._coef = torch.ones(1, dtype=torch.float32, device=self.device)
+            self._norm = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self._sq_scratch = torch.empty(N.sumsq_blocks(), dtype=torch.float32, device=self.device)
+
+    # ------------------------------------------------------------------ ParamProvider
+    def expect_passes(self, k: int) -> None:
+        """How many backward passes traverse each unit per micro-step (2 when chosen/rejected run as
+        separate forwards like ``R/src/training/train_dpo.py:113-114``)."""
+        self._passes_expected = max(1, int(k))
+
+    def _gather_async(self, unit: str) -> None:
+        if self.full.get(unit) is not None or unit in self._gather_work:
+            return
+        full = torch.empty(self.P[unit], dtype=self.dtype, device=self.device)
+        work = dist.all_gather_into_tensor(full, self.shard[unit], group=self.ctx.group, async_op=True)
+        self.stats["allgather_bytes"] += full.numel() * full.element_size()
+        self._gather_work[unit] = (work, full)
+
+    def _neighbour(self, unit: str, backward: bool) -> Optional[str]:
+        i = self._order.index(unit) + (-1 if backward else 1)
+        return self._order[i] if 0 <= i < len(self._order) else None
+
+    def acquire(self, unit: str, backward: bool = False) -> Weights:
+        if unit in self._views:
+            return self._views[unit]
+        if self.full.get(unit) is None:
+            self._gather_async(unit)
+            work, full = self._gather_work.pop(unit)
+            work.wait()
+            self.full[unit] = full
+            nxt = self._neighbour(unit, backward)
+            if nxt is not None:                      # one-unit-ahead prefetch overlaps this unit's math
+                self._gather_async(nxt)
+        spec = self._by_name[unit]
+        w = unit_views(self.full[unit], spec)
+        if self.trainable:
+            gb = self.gradbuf.get(unit)
+            if gb is None:
+                gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
+                self.gradbuf[unit] = gb
+            g = unit_views(gb, spec)
+            for k, t in w.items():
+                t.requires_grad_(True)
+                t._grad_slot = g[k]
+        self._views[unit] = w
+        return w
+
+    def release(self, unit: str, backward: bool = False) -> None:
+        if self.resident:
+            return
+        if self.trainable and not backward and torch.is_grad_enabled():
+            return                                  # non-checkpointed training keeps the unit for backward
+        self._views.pop(unit, None)
+        self.full[unit] = None
+
+    def grads_done(self, unit: str, weights: Weights) -> None:
+        collect_autograd_grads(weights)
+        if not self.trainable:
+            return
+        seen = self._passes_seen.get(unit, 0) + 1
+        self._passes_seen[unit] = seen
+        if seen < self._passes_expected:
+            return
+        self._passes_seen[unit] = 0
+        if self.ctx.world_size == 1:
+            return
+        if self.resident:
+            if self.sync_grads:
+                self._launch_reduce(unit)
+        else:
+            self._launch_reduce(unit)               # streamed units reduce-scatter every micro-step
+
+    def _launch_reduce(self, unit: str) -> None:
+        gb = self.gradbuf[unit]
+        nbytes = gb.numel() * gb.element_size()
+        self.stats["reduce_bytes"] += nbytes
+        if self.sharding == "ddp":
+            work = dist.all_reduce(gb, group=self.ctx.group, async_op=True)
+            self._reduce_work.append((work, unit, None))
+        else:
+            out = torch.empty(self.S[unit], dtype=gb.dtype, device=self.device)
+            work = dist.reduce_scatter_tensor(out, gb, group=self.ctx.group, async_op=True)
+            self._reduce_work.append((work, unit, out))
+            if not self.resident:
+                self._drain(keep=2)                 # bound live full-size grad buckets when streaming units
+
+    def _drain(self, keep: int = 0) -> None:
+        while len(self._reduce_work) > keep:
+            work, unit, out = self._reduce_work.pop(0)
+            work.wait()
+            if out is None:
+                continue
+            if self.resident:
+                S = self.S[unit]
+                self.gradbuf[unit][self.r * S:(self.r + 1) * S].copy_(out)
+            else:
+                self.gshard[unit].add_(out.float())
+                self.gradbuf[unit] = None
+                self._views.pop(unit, None)
+
+    def finish_backward(self) -> None:
+        """Call after ``loss.backward()``: sweeps stray autograd grads, waits for the reductions of this
+        micro-step and folds reduce-scatter outputs into the shard accumulators."""
+        for unit, w in list(self._views.items()):
+            collect_autograd_grads(w)
+        self._drain(0)
+
+    # ------------------------------------------------------------------ optimizer
+    def _local_grad(self, unit: str) -> torch.Tensor:
+        """The gradient values this rank's optimizer shard consumes (summed over ranks, not averaged)."""
+        if self.W == 1:
+            return self.gradbuf[unit]
+        if self.resident:
+            S = self.S[unit]
+            return self.gradbuf[unit][self.r * S:(self.r + 1) * S]
+        return self.gshard[unit]
+
+    def optimizer_step(self, opt: AdamWConfig, lr: Optional[float] = None, grad_divisor: float = 1.0) -> None:
+        """Global-norm clip + AdamW on the rank's shards, then refresh the bf16 parameters.
+
+        Gradients in the buckets are SUMS over ranks and micro-steps; ``grad_divisor`` (world x
+        accumulation steps) turns them into the mean the reference's DDP/accumulate produces."""
+        assert self.trainable
+        lr = opt.lr if lr is None else lr
+        self.step_count += 1
+        t = self.step_count
+        b1, b2 = opt.betas
+        bc1, bc2 = 1 - b1 ** t, 1 - b2 ** t
+        prescale = 1.0 / grad_divisor
+        cuda = self.device.type == "cuda"
+        # ---- global grad norm -------------------------------------------------------
+        if cuda:
+            s = N.stream_ptr(self.device)
+            self._sumsq.zero_()
+            for u in self.units:
+                g = self._local_grad(u.name)
+                N.call("dla_sumsq", N.ptr(g), g.numel(), int(g.dtype == torch.float32), N.ptr(self._sq_scratch),
+                       N.ptr(self._sumsq), 1, s)
+            if self.W > 1:
+                dist.all_reduce(self._sumsq, group=self.ctx.group)
+            self._sumsq.mul_(prescale * prescale)
+            N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
+            self.last_grad_norm = self._norm
+        else:
+            sq = torch.zeros((), dtype=torch.float64)
+            for u in self.units:
+                sq += self._local_grad(u.name).double().pow(2).sum()
+            if self.W > 1:
+                sq = sq.reshape(1)
+                dist.all_reduce(sq, group=self.ctx.group)
+                sq = sq.reshape(())
+            norm = float(sq.sqrt()) * prescale
+            coef = 1.0
+            if opt.max_grad_norm and opt.max_grad_norm > 0:
+                coef = min(1.0, opt.max_grad_norm / (norm + 1e-6))
+            if not math.isfinite(norm):
+                coef = 0.0
+            self.last_grad_norm = torch.tensor(norm)
+        # ---- update -----------------------------------------------------------------
+        for u in self.units:
+            g = self._local_grad(u.name)
+            sh = self.shard[u.name]
+            if cuda:
+                N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]), N.ptr(g),
+                       N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef),
+                       prescale, int(g.dtype == torch.float32), N.stream_ptr(self.device))
+            else:
+                R.adamw_step(self.master[u.name], self.m[u.name], self.v[u.name], g, lr, b1, b2, opt.eps,
+                             opt.weight_decay, t, grad_scale=prescale * coef)
+                sh.copy_(self.master[u.name].to(sh.dtype))
+        # ---- refresh resident gathered params ----------------------------------------
+        if self.W > 1 and self.resident:
+            works = []
+            for u in self.units:
+                works.append(dist.all_gather_into_tensor(self.full[u.name], self.shard[u.name], group=self.ctx.group, async_op=True))
+                self.stats["allgather_bytes"] += self.P[u.name] * _bytes(self.dtype)
+            for w in works:
+                w.wait()
+        self.zero_grad()
+
+    def zero_grad(self) -> None:
+        for k, g in self.gradbuf.items():
+            if g is not None:
+                g.zero_()
+        for g in self.gshard.values():
+            g.zero_()
+
+    # ------------------------------------------------------------------ state access
+    def num_params(self) -> int:
+        return sum(u.numel for u in self.units)
+
+    def gathered_unit(self, unit: str) -> Weights:
+        """Full (unsharded) views of a unit's parameters for export; collective when sharded."""
+        if self.full.get(unit) is not None:
+            return unit_views(self.full[unit], self._by_name[unit])
+        full = torch.empty(self.P[unit], dtype=self.dtype, device=self.device)
+        dist.all_gather_into_tensor(full, self.shard[unit], group=self.ctx.group)
+        return unit_views(full, self._by_name[unit])
+
+    def load_unit(self, unit: str, tensors: Dict[str, torch.Tensor]) -> None:
+        """Overwrite named parameters of a unit from full-size tensors (every rank passes the same)."""
+        spec = self._by_name[unit]
+        offs = spec.offsets()
+        S = self.S[unit]
+        lo, hi = self.r * S, (self.r + 1) * S
+        for name, t in tensors.items():
+            o, n = offs[name]
+            flat = t.reshape(-1).to(self.device, self.dtype)
+            if self.full.get(unit) is not None:
+                self.full[unit][o:o + n].copy_(flat)
+            if self.W > 1:
+                a, b = max(o, lo), min(o + n, hi)
+                if a < b:
+                    self.shard[unit][a - lo:b - lo].copy_(flat[a - o:b - o])
+        if self.trainable:
+            self.master[unit].copy_(self.shard[unit].float())
+
+    def shard_state(self) -> Dict[str, torch.Tensor]:
+        """This rank's exact-resume state: fp32 master + Adam moments per unit."""
+        out: Dict[str, torch.Tensor] = {}
+        for u in self.units:
+            if self.trainable:
+                out[f"{u.name}.master"] = self.master[u.name]
+                out[f"{u.name}.m"] = self.m[u.name]
+                out[f"{u.name}.v"] = self.v[u.name]
+            else:
+                out[f"{u.name}.param"] = self.shard[u.name]
+        return out
+
+    def load_shard_state(self, state: Dict[str, torch.Tensor], step_count: int) -> None:
+        for u in self.units:
+            if self.trainable and f"{u.name}.master" in state:
+                self.master[u.name].copy_(state[f"{u.name}.master"])
+                self.m[u.name].copy_(state[f"{u.name}.m"].to(self.state_dtype))
+                self.v[u.name].copy_(state[f"{u.name}.v"].to(self.state_dtype))
+                self.shard[u.name].copy_(self.master[u.name].to(self.dtype))
+            elif f"{u.name}.param" in state:
+                self.shard[u.name].copy_(state[f"{u.name}.param"].to(self.dtype))
+        self.step_count = step_count
+        if self.W > 1 and self.resident:
+            for u in self.units:
+                dist.all_gather_into_tensor(self.full[u.name], self.shard[u.name], group=self.ctx.group)
+
+    def memory_report(self) -> Dict[str, float]:
+        gb = 1 / (1 << 30)
+        tot = lambda d: sum(t.numel() * t.element_size() for t in d.values() if t is not None) * gb
+        own = tot(self.shard) if self.W > 1 else 0.0
+        return {"params_full_gb": tot(self.full), "params_shard_gb": own, "grads_gb": tot(self.gradbuf) + tot(self.gshard),
+                "optimizer_gb": tot(self.master) + tot(self.m) + tot(self.v)}
+
+
+def _bytes(dt: torch.dtype) -> int:
+    return torch.empty((), dtype=dt).element_size()
+
+
+def _default_budget(device: torch.device) -> int:
+    if device.type == "cuda":
+        free, total = torch.cuda.mem_get_info(device)
+        return int(total * 0.45)
+    return 1 << 62
