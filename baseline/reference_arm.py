@@ -43,10 +43,15 @@ def import_reference_fns():
         try:
             import accelerate  # noqa: F401
         except Exception:
+            import importlib.machinery
+
+            import transformers  # noqa: F401  (resolve its optional-dependency probes before the stand-in exists)
             acc = types.ModuleType("accelerate")
+            acc.__spec__ = importlib.machinery.ModuleSpec("accelerate", None)
             for n in ("Accelerator", "DeepSpeedPlugin", "FullyShardedDataParallelPlugin"):
                 setattr(acc, n, type(n, (), {}))
             util = types.ModuleType("accelerate.utils")
+            util.__spec__ = importlib.machinery.ModuleSpec("accelerate.utils", None)
             util.DistributedDataParallelKwargs = type("DistributedDataParallelKwargs", (), {"__init__": lambda self, **k: None})
             acc.utils = util
             sys.modules["accelerate"], sys.modules["accelerate.utils"] = acc, util

@@ -229,7 +229,9 @@ class _CheckpointedUnit(torch.autograd.Function):
     (so a sharded engine can launch that unit's reduce-scatter while earlier layers still run)."""
 
     @staticmethod
-    def forward(ctx, provider, unit, fn, *inputs):
+    def forward(ctx, provider, unit, fn, anchor, *inputs):
+        # ``anchor`` is a dummy scalar that requires grad: parameters are not autograd inputs of this
+        # Function, so without it a unit whose inputs carry no grad (the embedding) would cut the graph.
         ctx.provider, ctx.unit, ctx.fn = provider, unit, fn
         ctx.save_for_backward(*[t for t in inputs if isinstance(t, torch.Tensor)])
         ctx.layout = [isinstance(t, torch.Tensor) for t in inputs]
@@ -264,13 +266,24 @@ class _CheckpointedUnit(torch.autograd.Function):
         provider.grads_done(unit, w)
         provider.release(unit, backward=True)
         in_grads = tuple(t.grad if isinstance(t, torch.Tensor) and t.is_floating_point() else None for t in inputs)
-        return (None, None, None) + in_grads
+        return (None, None, None, None) + in_grads
+
+
+_ANCHORS: Dict[str, torch.Tensor] = {}
+
+
+def _anchor(device: torch.device) -> torch.Tensor:
+    key = str(device)
+    if key not in _ANCHORS:
+        _ANCHORS[key] = torch.zeros((), device=device, requires_grad=True)
+    return _ANCHORS[key]
 
 
 def run_unit(provider: ParamProvider, unit: str, fn: Callable, *inputs):
     grad_mode = torch.is_grad_enabled() and provider.trainable
     if grad_mode and provider.checkpoint:
-        return _CheckpointedUnit.apply(provider, unit, fn, *inputs)
+        dev = next(t.device for t in inputs if isinstance(t, torch.Tensor))
+        return _CheckpointedUnit.apply(provider, unit, fn, _anchor(dev), *inputs)
     w = provider.acquire(unit, backward=False)
     out = fn(w, *inputs)
     if not grad_mode:

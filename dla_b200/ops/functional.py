@@ -102,7 +102,8 @@ class _Linear(Function):
         ctx.bias_ref = bias
         ctx.wref = w
         ctx.xshape = x.shape
-        return y.view(*x.shape[:-1], w.shape[0])
+        # a 2-D input gets the GEMM output itself (not a view): callers may modify it in place (RoPE)
+        return y if x.dim() == 2 else y.view(*x.shape[:-1], w.shape[0])
 
     @staticmethod
     def backward(ctx, dy):

@@ -1,0 +1,126 @@
+#!/usr/bin/env python
+"""Per-kernel timing on one B200 with CUDA events (warm-up, L2 flush between iterations) and roofline
+fractions against MEASURED_PEAKS.json.  Writes JSON lines to gpurun_out/kernels.jsonl."""
+from __future__ import annotations
+
+import json
+import math
+import sys
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+from dla_b200.obs import measured_peaks  # noqa: E402
+from dla_b200.ops import functional as F  # noqa: E402
+from dla_b200.ops import native as N  # noqa: E402
+
+DEV = "cuda"
+PK = measured_peaks()
+FLUSH = None
+
+
+def timeit(fn, iters=10, warm=3, flush=True):
+    global FLUSH
+    if FLUSH is None:
+        FLUSH = torch.empty(256 << 20, dtype=torch.uint8, device=DEV)
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush:
+            FLUSH.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def rnd(*s):
+    return torch.randn(*s, device=DEV, dtype=torch.bfloat16)
+
+
+def main():
+    out = []
+    which = sys.argv[1:] or ["gemm", "attn", "elem", "logprob"]
+    if "gemm" in which:
+        shapes = [(8192, 6144, 4096, "qkv"), (8192, 4096, 4096, "wo"), (8192, 28672, 4096, "gate_up"), (8192, 4096, 14336, "down"),
+                  (8192, 8192, 8192, "square"), (4096, 128256, 4096, "lm_head"), (2048, 4096, 4096, "small_m")]
+        for M, Nn, K, tag in shapes:
+            a, b = rnd(M, K), rnd(Nn, K)
+            c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+            flops = 2.0 * M * Nn * K
+            t_own = timeit(lambda: F.gemm(a, b, out=c))
+            t_lib = timeit(lambda: torch.matmul(a, b.t(), out=c))
+            rec = {"kernel": "gemm_nt", "tag": tag, "M": M, "N": Nn, "K": K, "ms": t_own, "tflops": flops / t_own / 1e9,
+                   "cublas_ms": t_lib, "cublas_tflops": flops / t_lib / 1e9,
+                   "frac_of_measured_peak": flops / t_own / 1e9 / PK["bf16_tflops"]}
+            # dgrad (B mn-major) and wgrad (both mn-major) of the same Linear
+            dy = rnd(M, Nn)
+            dx = torch.empty(M, K, device=DEV, dtype=torch.bfloat16)
+            dw = torch.empty(Nn, K, device=DEV, dtype=torch.bfloat16)
+            rec["dgrad_tflops"] = flops / timeit(lambda: F.gemm(dy, b, b_mn=True, out=dx)) / 1e9
+            rec["wgrad_tflops"] = flops / timeit(lambda: F.gemm(dy, a, a_mn=True, b_mn=True, out=dw)) / 1e9
+            out.append(rec)
+            print(json.dumps(rec), flush=True)
+    if "attn" in which:
+        for B, T, Hq, Hk, D in [(8, 1024, 32, 8, 128), (2, 4096, 32, 8, 128)]:
+            qkv = rnd(B, T, Hq + 2 * Hk, D).requires_grad_()
+            q, k, v = qkv[:, :, :Hq], qkv[:, :, Hq:Hq + Hk], qkv[:, :, Hq + Hk:]
+            fl = 4.0 * B * Hq * T * T * D / 2
+            t_f = timeit(lambda: F.attention(q.detach(), k.detach(), v.detach()))
+            o = F.attention(q, k, v)
+            g = rnd(B, T, Hq, D)
+            t_b = timeit(lambda: torch.autograd.grad(o, qkv, g, retain_graph=True))
+            qs, ks, vs = (t.detach().transpose(1, 2).contiguous() for t in (q, k, v))
+            t_sdpa = timeit(lambda: torch.nn.functional.scaled_dot_product_attention(qs, ks, vs, is_causal=True, enable_gqa=True))
+            rec = {"kernel": "attention", "B": B, "T": T, "Hq": Hq, "Hk": Hk, "D": D, "fwd_ms": t_f, "fwd_tflops": fl / t_f / 1e9,
+                   "bwd_ms": t_b, "bwd_tflops": 2.5 * fl / t_b / 1e9, "sdpa_fwd_ms": t_sdpa, "sdpa_fwd_tflops": fl / t_sdpa / 1e9}
+            out.append(rec)
+            print(json.dumps(rec), flush=True)
+    if "elem" in which:
+        M, H, Fi = 8192, 4096, 14336
+        x, d, w = rnd(M, H), rnd(M, H), rnd(H)
+        t = timeit(lambda: F.add_rmsnorm(x, d, w, 1e-5))
+        rec = {"kernel": "add_rmsnorm_fwd", "M": M, "H": H, "ms": t, "gbs": 4 * M * H * 2 / t / 1e6, "frac_hbm": 4 * M * H * 2 / t / 1e6 / PK["hbm_gbs"]}
+        out.append(rec); print(json.dumps(rec), flush=True)
+        gu = rnd(M, 2 * Fi)
+        t = timeit(lambda: F.swiglu(gu))
+        rec = {"kernel": "swiglu_fwd", "M": M, "F": Fi, "ms": t, "gbs": 3 * M * Fi * 2 / t / 1e6, "frac_hbm": 3 * M * Fi * 2 / t / 1e6 / PK["hbm_gbs"]}
+        out.append(rec); print(json.dumps(rec), flush=True)
+        n = 218_112_000
+        master, m_, v_ = (torch.zeros(n, device=DEV) for _ in range(3))
+        g, p = torch.zeros(n, device=DEV, dtype=torch.bfloat16), torch.empty(n, device=DEV, dtype=torch.bfloat16)
+        t = timeit(lambda: N.call("dla_adamw", N.ptr(master), N.ptr(m_), N.ptr(v_), N.ptr(g), N.ptr(p), n, 1e-5, 0.9, 0.95, 1e-8, 0.01,
+                                  0.1, 0.05, None, 1.0, 0, N.stream_ptr()), flush=False)
+        rec = {"kernel": "adamw", "n": n, "ms": t, "gbs": n * 28 / t / 1e6, "frac_hbm": n * 28 / t / 1e6 / PK["hbm_gbs"]}
+        out.append(rec); print(json.dumps(rec), flush=True)
+    if "logprob" in which:
+        M, V, K = 8192, 128256, 4096
+        h, w = rnd(M, K), rnd(V, K) * 0.02
+        lab = torch.randint(0, V, (M,), device=DEV)
+        t = timeit(lambda: F.linear_logprob(h, w, lab), iters=5)
+        rec = {"kernel": "lmhead_logprob_fwd", "M": M, "V": V, "K": K, "ms": t, "tflops": 2.0 * M * V * K / t / 1e9}
+
+        def ref():
+            logits = torch.matmul(h, w.t())
+            lp = torch.log_softmax(logits.float(), -1)
+            return lp.gather(-1, lab[:, None])
+        t2 = timeit(ref, iters=3)
+        rec["reference_ms"] = t2
+        out.append(rec); print(json.dumps(rec), flush=True)
+    Path(ROOT / "gpurun_out").mkdir(exist_ok=True)
+    with open(ROOT / "gpurun_out" / "kernels.jsonl", "a") as fh:
+        for r in out:
+            fh.write(json.dumps(r) + "\n")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,36 @@
+#!/usr/bin/env python
+"""Tiny single-op drivers for ncu (one GPU, a handful of launches)."""
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from dla_b200.ops import functional as F  # noqa: E402
+
+what = sys.argv[1] if len(sys.argv) > 1 else "gemm"
+dev = "cuda"
+r = lambda *s: torch.randn(*s, device=dev, dtype=torch.bfloat16)
+if what == "gemm":
+    a, b = r(8192, 4096), r(14336 * 2, 4096)
+    for _ in range(3):
+        c = F.gemm(a, b)
+elif what == "gemm_wgrad":
+    dy, x = r(8192, 4096), r(8192, 14336)
+    for _ in range(3):
+        c = F.gemm(dy, x, a_mn=True, b_mn=True)
+elif what in ("attn_fwd", "attn_bwd"):
+    B, T, Hq, Hk, D = 4, 1024, 32, 8, 128
+    qkv = r(B, T, Hq + 2 * Hk, D).requires_grad_()
+    q, k, v = qkv[:, :, :Hq], qkv[:, :, Hq:Hq + Hk], qkv[:, :, Hq + Hk:]
+    for _ in range(3):
+        o = F.attention(q, k, v)
+        if what == "attn_bwd":
+            torch.autograd.grad(o, qkv, r(B, T, Hq, D))
+elif what == "lmhead":
+    h, w = r(4096, 4096), r(128256, 4096) * 0.02
+    lab = torch.randint(0, 128256, (4096,), device=dev)
+    for _ in range(2):
+        F.linear_logprob(h, w, lab)
+torch.cuda.synchronize()
+print("ok", what)
