@@ -1,0 +1,166 @@
+"""Distributed plumbing on CPU / gloo, world_size 2 (BASELINE.json config #1):
+sharded (ZeRO-3, resident and streamed) = ZeRO-2 = replicated (DDP) = single process on the same global
+batch; checkpoint save -> load round trip; GPT-2 small-shaped DPO runs end to end through the CLI."""
+import json
+import os
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _dpo_worker(rank, world, port, sharding, resident, steps, accum, out):
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    sys.path.insert(0, str(ROOT))
+    torch.set_num_threads(2)
+    from dla_b200.algo import dpo_step
+    from dla_b200.data.synthetic import synthetic_preference_batch
+    from dla_b200.models import CausalLM, build_units, resolve_model_config
+    from dla_b200.optim import AdamWConfig
+    from dla_b200.parallel.engine import Engine
+    from dla_b200.parallel.pg import init_distributed, shutdown
+
+    ctx = init_distributed(device="cpu")
+    cfg = resolve_model_config("tiny-gpt2")
+    units = build_units(cfg)
+    pol = Engine(cfg, units, ctx, sharding=sharding, trainable=True, checkpoint=True, dtype=torch.float32, seed=7, resident=resident)
+    ref = Engine(cfg, units, ctx, sharding=sharding, trainable=False, checkpoint=False, dtype=torch.float32, seed=7, resident=resident)
+    mp_, mr = CausalLM(cfg, pol), CausalLM(cfg, ref)
+    opt = AdamWConfig(lr=5e-3, weight_decay=0.01, max_grad_norm=1.0)
+    G = 4                                             # global pairs per micro-step
+    losses = []
+    for step in range(steps):
+        for a in range(accum):
+            full = synthetic_preference_batch(G, 12, cfg.vocab_size, seed=100 + step * accum + a, ragged=True)
+            lo, hi = rank * G // world, (rank + 1) * G // world
+            batch = {s: {k: v[lo:hi] for k, v in full[s].items()} for s in full}
+            pol.sync_grads = (a == accum - 1)
+            loss, _ = dpo_step(mp_, mr, batch, beta=0.5)
+            loss.backward()
+            pol.finish_backward()
+            losses.append(float(ctx.all_reduce(loss.detach().clone(), "mean")))
+        pol.optimizer_step(opt, grad_divisor=float(world * accum))
+    flat = torch.cat([pol.gathered_unit(u.name)[p.name].reshape(-1) for u in units for p in u.params])
+    if rank == 0:
+        torch.save({"losses": losses, "params": flat.clone(), "gnorm": float(pol.last_grad_norm)}, out)
+    shutdown()
+
+
+def _run(tmp_path, world, sharding, resident=None, steps=3, accum=1, tag=""):
+    out = tmp_path / f"res_{sharding}_{world}_{resident}_{accum}{tag}.pt"
+    port = _free_port()
+    if world == 1:
+        p = mp.get_context("spawn").Process(target=_dpo_worker, args=(0, 1, port, sharding, resident, steps, accum, str(out)))
+        p.start()
+        p.join(300)
+        assert p.exitcode == 0
+    else:
+        mp.spawn(_dpo_worker, args=(world, port, sharding, resident, steps, accum, str(out)), nprocs=world, join=True)
+    return torch.load(out)
+
+
+@pytest.mark.timeout(600)
+def test_sharded_replicated_single_agree(tmp_path):
+    single = _run(tmp_path, 1, "ddp")
+    ddp = _run(tmp_path, 2, "ddp")
+    z2 = _run(tmp_path, 2, "zero2")
+    z3 = _run(tmp_path, 2, "zero3", resident=True)
+    z3s = _run(tmp_path, 2, "zero3", resident=False)
+    assert single["losses"][0] == pytest.approx(0.693147, abs=1e-5)
+    assert single["losses"][-1] < single["losses"][0]
+    for name, res in (("ddp", ddp), ("zero2", z2), ("zero3", z3), ("zero3-streamed", z3s)):
+        assert res["losses"] == pytest.approx(single["losses"], abs=2e-5), name
+        assert torch.allclose(res["params"], single["params"], atol=2e-5), name
+        assert res["gnorm"] == pytest.approx(single["gnorm"], rel=1e-4), name
+
+
+@pytest.mark.timeout(600)
+def test_gradient_accumulation_matches_large_batch(tmp_path):
+    a = _run(tmp_path, 2, "zero3", resident=True, steps=2, accum=2, tag="acc")
+    b = _run(tmp_path, 2, "zero3", resident=False, steps=2, accum=2, tag="acc")
+    c = _run(tmp_path, 1, "ddp", steps=2, accum=2, tag="acc")
+    assert torch.allclose(a["params"], c["params"], atol=2e-5)
+    assert torch.allclose(b["params"], c["params"], atol=2e-5)
+
+
+def _ckpt_worker(rank, world, port, root):
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    sys.path.insert(0, str(ROOT))
+    torch.set_num_threads(2)
+    from dla_b200.ckpt import CheckpointManager, load_model_dir
+    from dla_b200.data import ByteTokenizer
+    from dla_b200.models import build_units, resolve_model_config
+    from dla_b200.optim import AdamWConfig
+    from dla_b200.parallel.engine import Engine
+    from dla_b200.parallel.pg import init_distributed, shutdown
+
+    ctx = init_distributed(device="cpu")
+    cfg = resolve_model_config("tiny-llama")
+    units = build_units(cfg)
+    eng = Engine(cfg, units, ctx, sharding="zero3", dtype=torch.float32, seed=3, resident=False, name="policy")
+    for u in units:       # fake one optimizer step so the moments are non-trivial
+        eng.gshard[u.name].normal_(generator=torch.Generator().manual_seed(rank))
+    eng.optimizer_step(AdamWConfig(lr=1e-2), grad_divisor=1.0)
+    mgr = CheckpointManager(root, ctx, keep_last_n=2)
+    for step in (1, 2, 3):
+        mgr.save(f"step_{step}", {"policy": eng}, {"global_step": step}, tokenizer=ByteTokenizer(512))
+    mgr.save("final", {"policy": eng}, {"global_step": 3}, tokenizer=ByteTokenizer(512))
+    # exact resume into a fresh engine
+    eng2 = Engine(cfg, units, ctx, sharding="zero3", dtype=torch.float32, seed=99, resident=False, name="policy")
+    state = mgr.load(mgr.resolve("latest"), {"policy": eng2})
+    assert state["global_step"] == 3 and eng2.step_count == 1
+    for u in units:
+        assert torch.equal(eng2.master[u.name], eng.master[u.name])
+        assert torch.equal(eng2.m[u.name], eng.m[u.name]) and torch.equal(eng2.v[u.name], eng.v[u.name])
+    # weights-only load through the HF-named safetensors into a REPLICATED engine (different layout)
+    eng3 = Engine(cfg, units, ctx, sharding="ddp", dtype=torch.float32, seed=5, trainable=False, name="other")
+    assert load_model_dir(eng3, Path(root) / "latest") > 0
+    for u in units:
+        a, b = eng.gathered_unit(u.name), eng3.gathered_unit(u.name)
+        for k in a:
+            assert torch.equal(a[k], b[k]), (u.name, k)
+    shutdown()
+
+
+@pytest.mark.timeout(600)
+def test_checkpoint_layout_roundtrip_and_keep_last_n(tmp_path):
+    root = tmp_path / "ckpt"
+    mp.spawn(_ckpt_worker, args=(2, _free_port(), str(root)), nprocs=2, join=True)
+    names = sorted(p.name for p in root.iterdir())
+    assert names == ["final", "latest", "step_2", "step_3"], names          # keep_last_n=2 pruned step_1
+    assert os.readlink(root / "latest") == "final"
+    for f in ("config.json", "generation_config.json", "model.safetensors", "trainer_state.json", "dla_tokenizer.json",
+              "shards/meta.json", "shards/rank_0.policy.safetensors", "shards/rank_1.policy.safetensors"):
+        assert (root / "final" / f).exists(), f
+    from dla_b200.models import resolve_model_config
+
+    assert resolve_model_config(str(root / "latest")).hidden_size == 256   # loadable as a model directory
+
+
+@pytest.mark.timeout(900)
+def test_gpt2_small_dpo_cli_gloo_world2(tmp_path):
+    """The shipped plumbing config end to end: launcher -> 2 gloo ranks -> ZeRO-3 GPT-2 small DPO."""
+    cfg = ROOT / "config" / "dpo_gpt2_cpu.yaml"
+    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="2")
+    cmd = [sys.executable, "-m", "dla_b200.cli.launch", "--cpu", "--nproc", "2", "--port", str(_free_port()), "-m",
+           "dla_b200.cli.train_dpo", "--config", str(cfg), "--override", f"logging.output_dir={tmp_path}/ck",
+           "--override", f"logging.log_dir={tmp_path}/logs", "--override", "optimization.max_train_steps=2",
+           "--override", "model.max_seq_length=32"]
+    res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=850)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert "DPO training complete" in res.stdout
+    lines = [json.loads(l) for l in (tmp_path / "logs" / "metrics.jsonl").read_text().splitlines()]
+    assert any("train/loss" in l for l in lines)
+    assert (tmp_path / "ck" / "latest" / "model.safetensors").exists()
