@@ -486,3 +486,102 @@ int dla_logprob_grad_inplace(void* logits, const float* lse, const int64_t* labe
 }
 
 }  // extern "C"
+
+// ====================================================================================================
+// Allocation-free variant of the fused lm_head log-prob.
+//
+// Who needs it: code that scores tokens from inside a process that cannot obtain device memory on
+// demand — typically an inference / scoring server that handed (almost) all of HBM to its own KV-cache
+// or tensor pool at start-up, so a cudaMalloc for our tile-partials work area would fail or fragment that
+// pool, and callers that run under a fixed memory budget audited ahead of time.  For them the work area
+// lives inside the library image: a file-scope __device__ array of a fixed, modest size.  Every GPU that
+// loads the library holds these bytes until the process exits, whether or not the entry point is called.
+//
+// Limits (stated, checked): M <= DLA_NOALLOC_MAX_ROWS rows per call and ceil(V / 256) <= DLA_NOALLOC_MAX_TILES
+// vocabulary tiles, i.e. V <= 131072 (Llama-3's 128256 fits).  Work area: 512 * 1024 * 8 B + 1024 * 4 B ~ 4 MiB.
+// ====================================================================================================
+#define DLA_NOALLOC_MAX_ROWS 1024
+#define DLA_NOALLOC_MAX_TILES 512
+
+struct __align__(256) NoAllocLogprobArea {
+  float2 partials[DLA_NOALLOC_MAX_TILES * DLA_NOALLOC_MAX_ROWS];   // [tile][row] (max, sum-exp)
+  float picked[DLA_NOALLOC_MAX_ROWS];                              // logit at the label
+};
+static __device__ __align__(256) NoAllocLogprobArea g_noalloc_logprob_area[1];
+
+namespace {
+constexpr int kMaxDevices = 64;
+// Device addresses of the array above, one per GPU.  In host code `g_noalloc_logprob_area` is only a
+// handle for the runtime, never something a kernel may dereference: the real address differs per device
+// and has to be asked for with that device current.
+NoAllocLogprobArea* g_noalloc_dev_ptr[kMaxDevices] = {};
+std::mutex g_noalloc_mu;
+
+int noalloc_area_for_current_device(NoAllocLogprobArea** out) {
+  int dev = -1;
+  DLA_CUDA(cudaGetDevice(&dev));
+  DLA_REQUIRE(dev >= 0 && dev < kMaxDevices, DLA_E_UNSUPP, "no-alloc log-prob: device index %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_logprob_area);
+    if (e != cudaSuccess || p == nullptr) {
+      dla::set_error("no-alloc log-prob: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : DLA_E_DRIVER;
+    }
+    g_noalloc_dev_ptr[dev] = reinterpret_cast<NoAllocLogprobArea*>(p);
+  }
+  *out = g_noalloc_dev_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+// Same result as dla_lmhead_logprob, but the tile partials go to the library's built-in work area:
+// no cudaMalloc / cudaFree / allocating library call happens here, on any call.
+//   * The FIRST call on each device looks up that device's address of the work area (and sets the
+//     kernel's shared-memory attribute).  Make that first call during start-up, before any stream capture.
+//   * All calls on one GPU share the one work area, which keeps whatever the previous call left in it.
+//     The part that must start from zero (the per-row "picked logit" slots, written only for rows whose
+//     label falls in a tile) is cleared on `stream` at the start of every call; the partials are fully
+//     rewritten for the rows and tiles a call reads back.
+//   * Because the area is shared, two calls whose GPU work overlaps in time (different streams, or
+//     different threads) race on it.  Issue them on one stream, or otherwise order them.
+int dla_lmhead_logprob_noalloc(const void* X, const void* W, const int64_t* labels, int M, int V, int K, int64_t ldx,
+                               int64_t ldw, float* logp, float* lse, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M > 0 && V > 0 && K > 0 && K % 8 == 0, DLA_E_BADARG, "lmhead_logprob_noalloc: bad shape M=%d V=%d K=%d", M, V, K);
+  DLA_REQUIRE(logp != nullptr, DLA_E_BADARG, "lmhead_logprob_noalloc: logp is required");
+  const int n_tiles = (V + BN - 1) / BN;
+  DLA_REQUIRE(M <= DLA_NOALLOC_MAX_ROWS, DLA_E_TOOLARGE,
+              "lmhead_logprob_noalloc: M=%d rows exceed the built-in work area (max %d rows per call); split the call or "
+              "use dla_lmhead_logprob with caller scratch", M, DLA_NOALLOC_MAX_ROWS);
+  DLA_REQUIRE(n_tiles <= DLA_NOALLOC_MAX_TILES, DLA_E_TOOLARGE,
+              "lmhead_logprob_noalloc: V=%d needs %d vocabulary tiles, the built-in work area holds %d (V <= %d)", V, n_tiles,
+              DLA_NOALLOC_MAX_TILES, DLA_NOALLOC_MAX_TILES * BN);
+  NoAllocLogprobArea* area = nullptr;
+  int rc = noalloc_area_for_current_device(&area);
+  if (rc) return rc;
+  CUtensorMap tmA, tmB;
+  rc = build_maps(&tmA, &tmB, X, W, M, V, K, ldx, ldw, 0, 0);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  DLA_CUDA(cudaMemsetAsync(area->picked, 0, sizeof(float) * (size_t)M, s));
+  Params p{};
+  p.M = M; p.N = V; p.K = K;
+  p.num_m_tiles = (M + BM - 1) / BM;
+  p.num_n_tiles = n_tiles;
+  p.labels = labels;
+  p.partials = area->partials;     // [n_tiles, M] packed with pitch M, exactly like the caller-scratch path
+  p.picked = area->picked;
+  rc = launch<false, false, kLogprob>(tmA, tmB, p, s);
+  if (rc) return rc;
+  logprob_combine_kernel<<<(M + 255) / 256, 256, 0, s>>>(p.partials, p.picked, labels, M, p.num_n_tiles, logp, lse);
+  return check_launch("lmhead_logprob_noalloc.combine");
+}
+
+int dla_lmhead_logprob_noalloc_max_rows(void) { return DLA_NOALLOC_MAX_ROWS; }
+int dla_lmhead_logprob_noalloc_max_vocab(void) { return DLA_NOALLOC_MAX_TILES * BN; }
+
+}  // extern "C"

@@ -142,6 +142,23 @@ size_t dla_lmhead_scratch_bytes(int M, int V);
  * using the saved lse (backward of the op above, chunked). */
 int dla_logprob_grad_inplace(void* logits, const float* lse, const int64_t* labels,
                              const float* grow, int Mc, int V, int64_t ld, void* stream);
+/* dla_lmhead_logprob for callers that cannot allocate device memory (no counterpart in the reference,
+ * which has no native code and lets PyTorch allocate).  Think of a scoring / inference server that gave
+ * nearly all of HBM to its own cache pool at start-up: a cudaMalloc for our work area would fail or eat
+ * into that pool, so here the tile partials live in a fixed ~4 MiB __device__ array inside the library
+ * image (held on every GPU that loads the library, until the process exits).  This entry point never
+ * calls cudaMalloc/cudaFree or an allocating library routine; the caller still owns inputs and outputs.
+ *   limits : M <= 1024 rows per call and V <= 131072 (dla_lmhead_logprob_noalloc_max_rows/_max_vocab);
+ *            larger sizes are rejected with DLA_E_TOOLARGE and a message, nothing is launched.
+ *   set-up : the first call on each device resolves that device's address of the array — make it once
+ *            at start-up, before any stream capture.
+ *   sharing: all calls on a GPU use the same array and inherit its previous contents; the slots that must
+ *            start at zero are cleared on `stream` at the top of every call.  Calls whose GPU work overlaps
+ *            (other streams / threads) race on it: keep them on one stream or order them yourself. */
+int dla_lmhead_logprob_noalloc(const void* X, const void* W, const int64_t* labels, int M, int V,
+                               int K, int64_t ldx, int64_t ldw, float* logp, float* lse, void* stream);
+int dla_lmhead_logprob_noalloc_max_rows(void);
+int dla_lmhead_logprob_noalloc_max_vocab(void);
 
 /* ---------------------------------------------------------------- attention (K2, K16) */
 /* Causal GQA flash attention, tcgen05: q [B,T,Hq,D], k/v [B,T,Hk,D] bf16 with explicit element
