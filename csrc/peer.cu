@@ -1,0 +1,315 @@
+// Collectives fused with their neighbouring compute, issued from inside the kernels over NVLink 5 /
+// NVSwitch peer memory (symmetric buffers: every rank holds device pointers to every peer's copy).
+//
+//   dla_peer_barrier      signal-pad barrier: st.release.sys flags into every peer, ld.acquire.sys spin
+//                         with a clock-based timeout (a dead peer must not hang the GPU forever)
+//   dla_fused_rs_adamw    (a) gradient reduce-scatter fused with cast/scale, the grad-norm partial and
+//                         (optionally) the sharded AdamW update + push of the updated bf16 shard into
+//                         every peer's resident parameter buffer (the post-step all-gather disappears)
+//   dla_peer_push         all-gather by P2P stores of an updated shard into all peers' buffers
+//   dla_fused_gather_dpo  (c) all-gather of per-sequence log-probs fused with the DPO loss and the
+//                         global preference-rate / margin reduction
+//
+// Reference equivalents: NCCL reduce_scatter / all_gather issued by FSDP/DeepSpeed under
+// accelerator.backward + clip_grad_norm_ + optimizer.step (R/src/training/train_dpo.py:118-121) and
+// rank-local ATen loss math (R/src/training/train_dpo.py:42-44, 130-132).
+#include "common.cuh"
+
+namespace dla {
+namespace peer {
+
+constexpr int kMaxWorld = 16;
+// set to 1 by any kernel whose wait on a peer flag timed out (dead / wedged peer); read with dla_peer_status()
+__device__ uint32_t g_peer_timeout_flag = 0;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// 16-byte load that bypasses L1 (peer data is written by another GPU; never reuse a stale line)
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void st_peer16(void* p, const uint4& v) {
+  asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// pads[r] -> rank r's pad: uint32 [channels][world].  Rank `me` publishes `epoch` into slot [channel][me]
+// of every peer, then waits until its own pad shows >= epoch from everyone.  status[0] is set to 1 on timeout.
+__device__ __forceinline__ bool barrier_body(uint32_t* const* pads, int world, int me, int channel, uint32_t epoch,
+                                             long long timeout_cycles) {
+  const int t = threadIdx.x;
+  bool ok = true;
+  if (t < world) {
+    __threadfence_system();
+    st_release_sys(pads[t] + channel * world + me, epoch);
+    const uint32_t* mine = pads[me] + channel * world + t;
+    const long long t0 = clock64();
+    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
+      if (timeout_cycles > 0 && clock64() - t0 > timeout_cycles) {
+        ok = false;
+        break;
+      }
+      __nanosleep(64);
+    }
+  }
+  return ok;
+}
+
+__global__ void barrier_kernel(uint32_t* const* pads, int world, int me, int channel, uint32_t epoch,
+                               long long timeout_cycles, uint32_t* status) {
+  const bool ok = barrier_body(pads, world, me, channel, epoch, timeout_cycles);
+  if (!ok) atomicExch(status != nullptr ? status : &g_peer_timeout_flag, 1u);
+}
+
+// ------------------------------------------------------------------------------- (a) RS + AdamW
+struct RsParams {
+  const bf16* const* peer_grads;   // [world] base pointers of every rank's full-size gradient bucket
+  bf16* const* peer_params;        // [world] base pointers of every rank's resident bf16 parameters (nullable)
+  int world, rank;
+  int64_t shard_elems, shard_offset;   // this rank's shard: elements [shard_offset, shard_offset + shard_elems)
+  float grad_scale;
+  float* grad_out;                 // fp32 [shard_elems] reduced + scaled gradient (modes 0/1)
+  float* sumsq_out;                // += sum(g^2) of the reduced, scaled gradient (mode 1)
+  float *master, *m, *v;           // fp32 [shard_elems] (mode 2)
+  float lr, beta1, beta2, eps, wd, inv_bc1, inv_sqrt_bc2;
+  const float* clip_coef;          // device scalar (nullable)
+  int mode;
+};
+
+template <int kMode>
+__global__ void __launch_bounds__(256)
+fused_rs_kernel(const RsParams p) {
+  __shared__ float red[33];
+  const int64_t nvec = p.shard_elems >> 3;
+  const float clip = (kMode == 2 && p.clip_coef != nullptr) ? *p.clip_coef : 1.f;
+  float ss = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = p.shard_offset + i * 8;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    // issue all peer loads first (NVLink latency ~2 us: keep world x 16 B in flight per thread)
+    uint4 raw[kMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < p.world) raw[r] = ld_peer16(p.peer_grads[(r + p.rank) % p.world] + e);
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < p.world) {
+        float f[8];
+        unpack8(*reinterpret_cast<const bf16x8*>(&raw[r]), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= p.grad_scale;
+    if (kMode <= 1) {
+      float* o = p.grad_out + i * 8;
+      *reinterpret_cast<float4*>(o) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+      *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+      if (kMode == 1) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += acc[j] * acc[j];
+      }
+    } else {
+      float w[8], mm[8], vv[8];
+      const int64_t o = i * 8;
+      *reinterpret_cast<float4*>(w) = *reinterpret_cast<const float4*>(p.master + o);
+      *reinterpret_cast<float4*>(w + 4) = *reinterpret_cast<const float4*>(p.master + o + 4);
+      *reinterpret_cast<float4*>(mm) = *reinterpret_cast<const float4*>(p.m + o);
+      *reinterpret_cast<float4*>(mm + 4) = *reinterpret_cast<const float4*>(p.m + o + 4);
+      *reinterpret_cast<float4*>(vv) = *reinterpret_cast<const float4*>(p.v + o);
+      *reinterpret_cast<float4*>(vv + 4) = *reinterpret_cast<const float4*>(p.v + o + 4);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float g = acc[j] * clip;
+        mm[j] = p.beta1 * mm[j] + (1.f - p.beta1) * g;
+        vv[j] = p.beta2 * vv[j] + (1.f - p.beta2) * g * g;
+        w[j] = w[j] * (1.f - p.lr * p.wd) - p.lr * p.inv_bc1 * (mm[j] / (sqrtf(vv[j]) * p.inv_sqrt_bc2 + p.eps));
+      }
+      *reinterpret_cast<float4*>(p.master + o) = *reinterpret_cast<float4*>(w);
+      *reinterpret_cast<float4*>(p.master + o + 4) = *reinterpret_cast<float4*>(w + 4);
+      *reinterpret_cast<float4*>(p.m + o) = *reinterpret_cast<float4*>(mm);
+      *reinterpret_cast<float4*>(p.m + o + 4) = *reinterpret_cast<float4*>(mm + 4);
+      *reinterpret_cast<float4*>(p.v + o) = *reinterpret_cast<float4*>(vv);
+      *reinterpret_cast<float4*>(p.v + o + 4) = *reinterpret_cast<float4*>(vv + 4);
+      if (p.peer_params != nullptr) {
+        const bf16x8 packed = pack8(w);
+        const uint4 u = *reinterpret_cast<const uint4*>(&packed);
+#pragma unroll
+        for (int r = 0; r < kMaxWorld; ++r)
+          if (r < p.world) st_peer16(p.peer_params[(r + p.rank) % p.world] + e, u);
+      }
+    }
+  }
+  if (kMode == 1) {
+    ss = block_sum(ss, red);
+    if (threadIdx.x == 0) atomicAdd(p.sumsq_out, ss);
+  }
+}
+
+// all-gather by stores: src[0..n) -> every peer's buffer at element offset dst_offset
+__global__ void __launch_bounds__(256)
+peer_push_kernel(const bf16* __restrict__ src, bf16* const* peers, int world, int rank, int64_t dst_offset, int64_t n) {
+  const int64_t nvec = n >> 3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint4 u = *reinterpret_cast<const uint4*>(src + i * 8);
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < world) st_peer16(peers[(r + rank) % world] + dst_offset + i * 8, u);
+  }
+}
+
+// ------------------------------------------------------------------------------- (c) gather + DPO loss
+__device__ __forceinline__ float log_sigmoid(float z) { return fminf(z, 0.f) - log1pf(__expf(-fabsf(z))); }
+__device__ __forceinline__ float sigmoid_(float z) { return 1.f / (1.f + __expf(-z)); }
+
+// peer_bufs[r]: fp32 [world][4][Bmax] on rank r.  Single block.
+__global__ void __launch_bounds__(256)
+fused_gather_dpo_kernel(float* const* peer_bufs, uint32_t* const* pads, int world, int me, const float* pp, const float* pn,
+                        const float* rp, const float* rn, int B, int Bmax, float beta, float ls, uint32_t epoch, int channel,
+                        long long timeout_cycles, float* out, float* dpp, float* dpn, uint32_t* status) {
+  __shared__ float red[33];
+  __shared__ int s_ok;
+  // 1. publish my [4, B] block into every peer's gather buffer (slot `me`)
+  for (int idx = threadIdx.x; idx < 4 * B; idx += blockDim.x) {
+    const int which = idx / B, i = idx % B;
+    const float v = which == 0 ? pp[i] : which == 1 ? pn[i] : which == 2 ? rp[i] : rn[i];
+    for (int r = 0; r < world; ++r) {
+      float* dst = peer_bufs[r] + ((int64_t)me * 4 + which) * Bmax + i;
+      asm volatile("st.global.relaxed.sys.f32 [%0], %1;" ::"l"(dst), "f"(v) : "memory");
+    }
+  }
+  __syncthreads();
+  // 2. flag exchange: everyone's block has landed in my buffer once all flags show this epoch
+  const bool ok = barrier_body(pads, world, me, channel, epoch, timeout_cycles);
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
+  if (!ok) s_ok = 0;
+  __syncthreads();
+  if (!s_ok) {
+    if (threadIdx.x == 0) atomicExch(status != nullptr ? status : &g_peer_timeout_flag, 1u);
+    return;
+  }
+  // 3. global statistics over world * B pairs, local gradients for my B pairs
+  const float* mine = peer_bufs[me];
+  float loss = 0.f, pref = 0.f, margin = 0.f;
+  const int total = world * B;
+  for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+    const int r = idx / B, i = idx % B;
+    const float* blk = mine + (int64_t)r * 4 * Bmax;
+    float a, b, c, d;
+    asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(a) : "l"(blk + i) : "memory");
+    asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(b) : "l"(blk + Bmax + i) : "memory");
+    asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(c) : "l"(blk + 2 * Bmax + i) : "memory");
+    asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(d) : "l"(blk + 3 * Bmax + i) : "memory");
+    const float z = beta * ((a - b) - (c - d));
+    loss += -(1.f - ls) * log_sigmoid(z) - ls * log_sigmoid(-z);
+    pref += a > b ? 1.f : 0.f;
+    margin += z;
+    if (r == me) {
+      // gradient of the LOCAL-batch mean (the engine divides by world when it averages over ranks)
+      const float dz = (-(1.f - ls) * sigmoid_(-z) + ls * sigmoid_(z)) * beta / (float)B;
+      dpp[i] = dz;
+      dpn[i] = -dz;
+    }
+  }
+  loss = block_sum(loss, red);
+  pref = block_sum(pref, red);
+  margin = block_sum(margin, red);
+  if (threadIdx.x == 0) {
+    const float inv = 1.f / (float)total;
+    out[0] = loss * inv;      // global mean loss
+    out[1] = pref * inv;      // global preference rate
+    out[2] = margin * inv;    // global mean margin
+  }
+}
+
+static long long timeout_cycles(int timeout_ms) {
+  return timeout_ms > 0 ? (long long)timeout_ms * 1900000LL : 0;   // ~1.9 GHz SM clock
+}
+
+}  // namespace peer
+}  // namespace dla
+
+using namespace dla;
+using namespace dla::peer;
+
+extern "C" {
+
+int dla_peer_barrier(uint32_t* const* pads, int world, int rank, int channel, uint32_t epoch, int timeout_ms, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, DLA_E_BADARG, "peer_barrier: bad world/rank %d/%d", world, rank);
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pads, world, rank, channel, epoch, timeout_cycles(timeout_ms),
+                                                    nullptr);
+  return check_launch("peer_barrier");
+}
+
+int dla_peer_status(int* timed_out) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  uint32_t v = 0;
+  DLA_CUDA(cudaMemcpyFromSymbol(&v, g_peer_timeout_flag, sizeof(v)));
+  *timed_out = (int)v;
+  return 0;
+}
+
+int dla_fused_rs_adamw(const void* const* peer_grads, void* const* peer_params, int world, int rank, int64_t shard_elems,
+                       int64_t shard_offset, float grad_scale, float* grad_out_fp32, float* sumsq_out, float* master, float* m,
+                       float* v, float lr, float beta1, float beta2, float eps, float weight_decay, float bias_c1, float bias_c2,
+                       const float* clip_coef_dev, int mode, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, DLA_E_BADARG, "fused_rs: bad world/rank %d/%d", world, rank);
+  DLA_REQUIRE(shard_elems % 8 == 0 && shard_offset % 8 == 0, DLA_E_BADARG, "fused_rs: shard size/offset must be multiples of 8 elements");
+  DLA_REQUIRE(mode >= 0 && mode <= 2, DLA_E_BADARG, "fused_rs: mode %d", mode);
+  DLA_REQUIRE(mode == 2 ? (master && m && v && bias_c1 > 0 && bias_c2 > 0) : (grad_out_fp32 != nullptr), DLA_E_BADARG,
+              "fused_rs: missing buffers for mode %d", mode);
+  DLA_REQUIRE(mode != 1 || sumsq_out != nullptr, DLA_E_BADARG, "fused_rs: sumsq_out required in mode 1");
+  if (shard_elems == 0) return 0;
+  RsParams p{};
+  p.peer_grads = reinterpret_cast<const bf16* const*>(peer_grads);
+  p.peer_params = reinterpret_cast<bf16* const*>(peer_params);
+  p.world = world; p.rank = rank; p.shard_elems = shard_elems; p.shard_offset = shard_offset; p.grad_scale = grad_scale;
+  p.grad_out = grad_out_fp32; p.sumsq_out = sumsq_out; p.master = master; p.m = m; p.v = v;
+  p.lr = lr; p.beta1 = beta1; p.beta2 = beta2; p.eps = eps; p.wd = weight_decay;
+  if (mode == 2) { p.inv_bc1 = 1.f / bias_c1; p.inv_sqrt_bc2 = 1.f / sqrtf(bias_c2); }
+  p.clip_coef = clip_coef_dev; p.mode = mode;
+  int64_t blocks = ((shard_elems >> 3) + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (mode == 0) fused_rs_kernel<0><<<(int)blocks, 256, 0, s>>>(p);
+  else if (mode == 1) fused_rs_kernel<1><<<(int)blocks, 256, 0, s>>>(p);
+  else fused_rs_kernel<2><<<(int)blocks, 256, 0, s>>>(p);
+  return check_launch("fused_rs_adamw");
+}
+
+int dla_peer_push(const void* src, void* const* peers, int world, int rank, int64_t dst_offset, int64_t n, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && n % 8 == 0 && dst_offset % 8 == 0, DLA_E_BADARG, "peer_push: bad arguments");
+  if (n == 0) return 0;
+  int64_t blocks = ((n >> 3) + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
+  peer_push_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)src, reinterpret_cast<bf16* const*>(peers), world, rank, dst_offset, n);
+  return check_launch("peer_push");
+}
+
+int dla_fused_gather_dpo(float* const* peer_bufs, uint32_t* const* pads, int world, int rank, const float* pol_pos,
+                         const float* pol_neg, const float* ref_pos, const float* ref_neg, int B, float beta,
+                         float label_smoothing, uint32_t epoch, float* out, float* dpol_pos, float* dpol_neg, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world && B > 0 && B <= 1024, DLA_E_BADARG,
+              "fused_gather_dpo: bad world/rank/B %d/%d/%d", world, rank, B);
+  fused_gather_dpo_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(peer_bufs, pads, world, rank, pol_pos, pol_neg, ref_pos, ref_neg, B,
+                                                              1024, beta, label_smoothing, epoch, /*channel=*/1,
+                                                              timeout_cycles(20000), out, dpol_pos, dpol_neg, nullptr);
+  return check_launch("fused_gather_dpo");
+}
+
+}  // extern "C"

@@ -70,7 +70,15 @@ def dpo_step(policy: CausalLM, ref: CausalLM, batch: Dict[str, Dict[str, torch.T
         with torch.no_grad():   # the reference forgets no_grad here (defect D16); the math is identical
             ref_pos = sequence_logprobs(ref, ch["input_ids"], ch["attention_mask"], reduction)
             ref_neg = sequence_logprobs(ref, rj["input_ids"], rj["attention_mask"], reduction)
-    loss, stats = F.dpo_loss(pol_pos, pol_neg, ref_pos, ref_neg, beta, label_smoothing, loss_scale)
+    eng = policy.p
+    if getattr(eng, "fused", False) and pol_pos.is_cuda and torch.is_grad_enabled():
+        # fused path (c): the cross-rank gather of the four log-prob vectors happens inside the loss kernel
+        # over NVLink peer memory; loss / preference rate / margin are GLOBAL-batch statistics
+        from dla_b200.parallel.fused import fused_dpo_loss
+
+        loss, stats = fused_dpo_loss(eng.fc, pol_pos, pol_neg, ref_pos, ref_neg, beta, label_smoothing)
+    else:
+        loss, stats = F.dpo_loss(pol_pos, pol_neg, ref_pos, ref_neg, beta, label_smoothing, loss_scale)
     info = {"pol_pos": pol_pos.detach(), "pol_neg": pol_neg.detach(), "ref_pos": ref_pos.detach(),
             "ref_neg": ref_neg.detach(), "preference_rate": stats[0], "margin": stats[1]}
     return loss, info

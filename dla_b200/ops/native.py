@@ -52,6 +52,7 @@ _SIGNATURES = {
     "dla_sample_top_p": [P, I, I, I, I64, F, F, c_uint64, c_uint64, P, P, P],
     "dla_fused_rs_adamw": [P, P, I, I, I64, I64, F, P, P, P, P, P, F, F, F, F, F, F, F, P, I, P],
     "dla_peer_barrier": [P, I, I, I, c_uint32, I, P],
+    "dla_peer_push": [P, P, I, I, I64, I64, P],
     "dla_fused_gather_dpo": [P, P, I, I, P, P, P, P, I, F, F, c_uint32, P, P, P, P],
 }
 

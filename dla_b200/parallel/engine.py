@@ -73,6 +73,18 @@ class Engine(ParamProvider):
             budget = hbm_budget_bytes if hbm_budget_bytes is not None else _default_budget(self.device)
             resident = self.sharding != "zero3" or need <= budget
         self.resident = bool(resident) or self.W == 1
+        # fused peer-memory collectives: sharded + resident + trainable on NVLink-connected CUDA ranks
+        self.fused = False
+        if comm in ("auto", "fused") and trainable and self.W > 1 and self.resident:
+            from dla_b200.parallel.fused import FusedComm, fused_available
+
+            if fused_available(ctx):
+                self.fused = True
+                self.fc = FusedComm.get(ctx)
+            elif comm == "fused":
+                raise RuntimeError("hardware.comm=fused needs >= 2 CUDA ranks on NCCL with the native library built")
+        self.gred: Dict[str, torch.Tensor] = {}
+        self.base: Dict[str, int] = {}
         self.full: Dict[str, Optional[torch.Tensor]] = {}
         self.shard: Dict[str, torch.Tensor] = {}
         self.gradbuf: Dict[str, Optional[torch.Tensor]] = {}
@@ -95,9 +107,24 @@ class Engine(ParamProvider):
 
     # ------------------------------------------------------------------ construction
     def _build(self, seed: int, init: bool) -> None:
+        if self.fused:
+            # parameters and gradient buckets of ALL units live in two symmetric arenas so that peers can
+            # read gradient shards and write updated parameter shards directly over NVLink
+            from dla_b200.parallel.fused import SymmetricArena
+
+            off = 0
+            for u in self.units:
+                self.base[u.name] = off
+                off += self.P[u.name]
+            self.param_arena = SymmetricArena(self.ctx, off, self.dtype)
+            self.grad_arena = SymmetricArena(self.ctx, off, self.grad_dtype)
         for ui, u in enumerate(self.units):
             P, S = self.P[u.name], self.S[u.name]
-            full = torch.zeros(P, dtype=self.dtype, device=self.device)
+            if self.fused:
+                b = self.base[u.name]
+                full = self.param_arena.tensor[b:b + P]
+            else:
+                full = torch.zeros(P, dtype=self.dtype, device=self.device)
             if init:
                 gen = torch.Generator(device=self.device).manual_seed(seed * 1000003 + ui)
                 init_unit_(full, u, self.cfg, gen)
@@ -108,7 +135,11 @@ class Engine(ParamProvider):
                 self.shard[u.name] = full            # the rank owns the whole unit
                 self.full[u.name] = full
             if self.trainable:
-                self.gradbuf[u.name] = torch.zeros(P, dtype=self.grad_dtype, device=self.device) if self.resident else None
+                if self.fused:
+                    self.gradbuf[u.name] = self.grad_arena.tensor[self.base[u.name]:self.base[u.name] + P]
+                    self.gred[u.name] = torch.zeros(S, dtype=torch.float32, device=self.device)
+                else:
+                    self.gradbuf[u.name] = torch.zeros(P, dtype=self.grad_dtype, device=self.device) if self.resident else None
                 if self.W > 1 and not self.resident:
                     self.gshard[u.name] = torch.zeros(S, dtype=torch.float32, device=self.device)
             del full
@@ -196,6 +227,8 @@ class Engine(ParamProvider):
             self._launch_reduce(unit)               # streamed units reduce-scatter every micro-step
 
     def _launch_reduce(self, unit: str) -> None:
+        if self.fused:
+            return          # peers pull this bucket themselves inside the fused kernel (optimizer_step)
         gb = self.gradbuf[unit]
         nbytes = gb.numel() * gb.element_size()
         self.stats["reduce_bytes"] += nbytes
@@ -229,6 +262,8 @@ class Engine(ParamProvider):
         for unit, w in list(self._views.items()):
             collect_autograd_grads(w)
         self._drain(0)
+        if self.fused and self.sync_grads:
+            self.fc.barrier(0)      # every rank's gradient buckets are complete before anyone reads them
 
     # ------------------------------------------------------------------ optimizer
     def _local_grad(self, unit: str) -> torch.Tensor:
@@ -253,6 +288,8 @@ class Engine(ParamProvider):
         bc1, bc2 = 1 - b1 ** t, 1 - b2 ** t
         prescale = 1.0 / grad_divisor
         cuda = self.device.type == "cuda"
+        if self.fused:
+            return self._fused_optimizer_step(opt, lr, prescale, bc1, bc2)
         # ---- global grad norm -------------------------------------------------------
         if cuda:
             s = N.stream_ptr(self.device)
@@ -301,6 +338,39 @@ class Engine(ParamProvider):
                 self.stats["allgather_bytes"] += self.P[u.name] * _bytes(self.dtype)
             for w in works:
                 w.wait()
+        self.zero_grad()
+
+    def _fused_optimizer_step(self, opt: AdamWConfig, lr: float, prescale: float, bc1: float, bc2: float) -> None:
+        """Fused path (a): per unit ONE kernel pulls this rank's gradient shard from every peer over NVLink,
+        sums in fp32, scales and accumulates the grad-norm partial; after the 4-byte norm all-reduce the
+        AdamW kernel consumes the fp32 shard and a peer-store kernel writes the updated bf16 shard into
+        every rank's resident parameters.  Without clipping the three collapse into one kernel."""
+        fc, s = self.fc, N.stream_ptr(self.device)
+        b1, b2 = opt.betas
+        clip_on = bool(opt.max_grad_norm and opt.max_grad_norm > 0)
+        if clip_on:
+            self._sumsq.zero_()
+            for u in self.units:
+                off = self.base[u.name] + self.r * self.S[u.name]
+                fc.reduce_shard(self.grad_arena, off, self.S[u.name], prescale, self.gred[u.name], self._sumsq)
+                self.stats["reduce_bytes"] += self.S[u.name] * _bytes(self.grad_dtype) * (self.W - 1)
+            dist.all_reduce(self._sumsq, group=self.ctx.group)
+            N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm), N.ptr(self._coef), N.ptr(self._norm), s)
+            self.last_grad_norm = self._norm
+            for u in self.units:
+                sh, off = self.shard[u.name], self.base[u.name] + self.r * self.S[u.name]
+                N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]),
+                       N.ptr(self.gred[u.name]), N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2,
+                       N.ptr(self._coef), 1.0, 1, s)
+                fc.push_shard(sh, self.param_arena, off)
+                self.stats["allgather_bytes"] += sh.numel() * _bytes(self.dtype) * (self.W - 1)
+        else:
+            for u in self.units:
+                off = self.base[u.name] + self.r * self.S[u.name]
+                fc.reduce_adamw_push(self.grad_arena, self.param_arena, off, self.S[u.name], prescale, self.master[u.name],
+                                     self.m[u.name], self.v[u.name], lr, (b1, b2), opt.eps, opt.weight_decay, bc1, bc2, None)
+            self.last_grad_norm = None
+        fc.barrier(0)               # all peers finished reading my gradients and writing my parameters
         self.zero_grad()
 
     def zero_grad(self) -> None:

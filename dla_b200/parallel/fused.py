@@ -1,0 +1,141 @@
+"""Peer-memory substrate and the fused compute+collective paths (BASELINE.json (a) and (c)).
+
+Symmetric buffers come from ``torch.distributed._symmetric_memory`` (cuMem + handle exchange done by torch:
+that is plumbing); what runs on them is ours: ``csrc/peer.cu`` kernels that load/store peer HBM over
+NVLink 5 / NVSwitch directly and synchronise with system-scope flags.
+
+    (a) gradient reduce-scatter + cast/scale + grad-norm partial (+ AdamW + push of the updated shard into
+        every peer's resident parameters): :meth:`FusedComm.reduce_shard`, :meth:`FusedComm.push_shard`
+    (c) cross-rank gather of sequence log-probs + DPO loss / preference-rate / margin: :meth:`FusedComm.dpo_loss`
+
+NCCL equivalents replaced: ``reduce_scatter_tensor`` + ``all_gather_into_tensor`` per unit per step
+ and nothing at all for C12 (the reference logs rank-local statistics).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from dla_b200.ops import native as N
+from dla_b200.parallel.pg import DistContext
+
+PAD_WORDS = 4096           # uint32 flag words per rank (channels x world)
+DPO_BMAX = 1024
+
+
+def fused_available(ctx: DistContext) -> bool:
+    if ctx.world_size < 2 or ctx.device.type != "cuda" or ctx.backend != "nccl":
+        return False
+    try:
+        import torch.distributed._symmetric_memory as symm  # noqa: F401
+        return N.available() and N.has("dla_fused_rs_adamw")
+    except Exception:
+        return False
+
+
+class SymmetricArena:
+    """One symmetric allocation visible to every rank; ``ptrs_dev`` is the address of a device array of
+    ``world`` base pointers (rank order) that kernels index to reach a peer's copy."""
+
+    def __init__(self, ctx: DistContext, numel: int, dtype: torch.dtype, zero: bool = True) -> None:
+        import torch.distributed._symmetric_memory as symm
+
+        self.ctx = ctx
+        self.tensor = symm.empty(numel, dtype=dtype, device=ctx.device)
+        if zero:
+            self.tensor.zero_()
+        self.handle = symm.rendezvous(self.tensor, ctx.group)
+        self.ptrs_dev = int(self.handle.buffer_ptrs_dev)
+        self.ptrs = list(self.handle.buffer_ptrs)
+        torch.cuda.synchronize(ctx.device)
+        ctx.barrier()
+
+
+class FusedComm:
+    _instances: Dict[int, "FusedComm"] = {}
+
+    def __init__(self, ctx: DistContext) -> None:
+        self.ctx = ctx
+        self.W, self.r = ctx.world_size, ctx.rank
+        self.pads = SymmetricArena(ctx, PAD_WORDS, torch.int32)
+        self.dpo_buf = SymmetricArena(ctx, self.W * 4 * DPO_BMAX, torch.float32)
+        self._epoch = [0] * 8
+
+    @classmethod
+    def get(cls, ctx: DistContext) -> "FusedComm":
+        key = id(ctx)
+        if key not in cls._instances:
+            cls._instances[key] = FusedComm(ctx)
+        return cls._instances[key]
+
+    # ---------------------------------------------------------------- barrier
+    def barrier(self, channel: int = 0, timeout_ms: int = 30000) -> None:
+        """All ranks' work enqueued before this point (on the current stream) is complete and visible to
+        peers before any rank's work enqueued after it starts."""
+        self._epoch[channel] += 1
+        N.call("dla_peer_barrier", self.pads.ptrs_dev, self.W, self.r, channel, self._epoch[channel], timeout_ms,
+               N.stream_ptr(self.ctx.device))
+
+    def check(self) -> None:
+        import ctypes
+
+        out = ctypes.c_int(0)
+        rc = N.load().dla_peer_status(ctypes.byref(out))
+        if rc != 0 or out.value != 0:
+            raise RuntimeError("a peer-flag wait timed out: a rank is dead or wedged (see dla_peer_status)")
+
+    # ---------------------------------------------------------------- (a)
+    def reduce_shard(self, grads: SymmetricArena, offset: int, n: int, scale: float, out_fp32: torch.Tensor,
+                     sumsq: Optional[torch.Tensor]) -> None:
+        """out[0:n) = scale * sum_r grads_r[offset : offset+n) read over NVLink; sumsq += sum(out^2)."""
+        N.call("dla_fused_rs_adamw", grads.ptrs_dev, None, self.W, self.r, n, offset, scale, N.ptr(out_fp32),
+               N.ptr(sumsq), None, None, None, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0, 1.0, None, 1 if sumsq is not None else 0,
+               N.stream_ptr(self.ctx.device))
+
+    def reduce_adamw_push(self, grads: SymmetricArena, params: SymmetricArena, offset: int, n: int, scale: float,
+                          master: torch.Tensor, m: torch.Tensor, v: torch.Tensor, lr: float, betas: Tuple[float, float],
+                          eps: float, wd: float, bc1: float, bc2: float, clip: Optional[torch.Tensor]) -> None:
+        """One kernel: reduce the shard over NVLink, AdamW it, store the new bf16 values into every rank's
+        resident parameters (no separate all-gather)."""
+        N.call("dla_fused_rs_adamw", grads.ptrs_dev, params.ptrs_dev, self.W, self.r, n, offset, scale, None, None,
+               N.ptr(master), N.ptr(m), N.ptr(v), lr, betas[0], betas[1], eps, wd, bc1, bc2, N.ptr(clip), 2,
+               N.stream_ptr(self.ctx.device))
+
+    def push_shard(self, src: torch.Tensor, params: SymmetricArena, offset: int) -> None:
+        N.call("dla_peer_push", N.ptr(src), params.ptrs_dev, self.W, self.r, offset, src.numel(), N.stream_ptr(self.ctx.device))
+
+    # ---------------------------------------------------------------- (c)
+    def dpo_loss(self, pol_pos, pol_neg, ref_pos, ref_neg, beta: float, label_smoothing: float):
+        """Returns (global stats [loss, pref_rate, margin], dpos, dneg) — gradients are of the local-batch mean."""
+        B = pol_pos.numel()
+        assert B <= DPO_BMAX
+        dev = pol_pos.device
+        out = torch.empty(3, dtype=torch.float32, device=dev)
+        dpp, dpn = torch.empty(B, dtype=torch.float32, device=dev), torch.empty(B, dtype=torch.float32, device=dev)
+        self._epoch[1] += 1
+        N.call("dla_fused_gather_dpo", self.dpo_buf.ptrs_dev, self.pads.ptrs_dev, self.W, self.r, N.ptr(pol_pos), N.ptr(pol_neg),
+               N.ptr(ref_pos), N.ptr(ref_neg), B, beta, label_smoothing, self._epoch[1], N.ptr(out), N.ptr(dpp), N.ptr(dpn),
+               N.stream_ptr(dev))
+        return out, dpp, dpn
+
+
+class _FusedDPOLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, comm, pp, pn, rp, rn, beta, ls):
+        pp, pn, rp, rn = (t.detach().float().contiguous() for t in (pp, pn, rp, rn))
+        out, dpp, dpn = comm.dpo_loss(pp, pn, rp, rn, beta, ls)
+        ctx.save_for_backward(dpp, dpn)
+        # the loss VALUE is the global mean; its gradient (below) is that of the local mean, which the
+        # engine's divide-by-world turns into the global-mean gradient
+        return out[0], out[1:].detach()
+
+    @staticmethod
+    def backward(ctx, g, _gs):
+        dpp, dpn = ctx.saved_tensors
+        return None, dpp * g, dpn * g, None, None, None, None
+
+
+def fused_dpo_loss(comm: FusedComm, pol_pos, pol_neg, ref_pos, ref_neg, beta: float, label_smoothing: float = 0.0):
+    return _FusedDPOLoss.apply(comm, pol_pos, pol_neg, ref_pos, ref_neg, beta, label_smoothing)

@@ -204,10 +204,16 @@ int dla_fused_rs_adamw(const void* const* peer_grads, void* const* peer_params, 
                        float lr, float beta1, float beta2, float eps, float weight_decay,
                        float bias_c1, float bias_c2, const float* clip_coef_dev, int mode,
                        void* stream);
+/* All-gather by peer stores: src[0..n) (bf16) -> element offset dst_offset of every rank's buffer
+ * (peers: device array of `world` base pointers).  n and dst_offset multiples of 8. */
+int dla_peer_push(const void* src, void* const* peers, int world, int rank, int64_t dst_offset,
+                  int64_t n, void* stream);
 /* Signal-pad barrier across ranks (system-scope release/acquire flags in peer memory).
  * pads: device array of W pointers to each rank's uint32 pad [W * channels]. */
 int dla_peer_barrier(uint32_t* const* pads, int world, int rank, int channel, uint32_t epoch,
                      int timeout_ms, void* stream);
+/* 1 if any peer-flag wait of this process timed out since load (synchronises the device). */
+int dla_peer_status(int* timed_out);
 /* (b) all-gather fused GEMM: C[M,N] = A[M,K] * Wfull[N,K]^T where Wfull's rows are sharded across
  * ranks (rank r owns rows [r*N/W, (r+1)*N/W)); B tiles are TMA-loaded straight from the owning
  * peer's memory (peer_maps built over peer pointers) into the tcgen05 pipeline. */
