@@ -22,7 +22,8 @@ namespace attn {
 
 constexpr int BQ = 128;
 constexpr int BKV = 128;
-constexpr int kThreads = 192;
+constexpr int kThreads = 192;        // backward: TMA warp, MMA warp, 4 row-owner warps
+constexpr int kFwdThreads = 320;     // forward: TMA warp, MMA warp, 2 x 4 softmax warps
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -51,6 +52,12 @@ __device__ __forceinline__ uint32_t sw128_offset(int row, int col) {
   return (uint32_t)(blk * 16384 + row * 128 + ((chunk ^ (row & 7)) << 4) + ((col & 7) << 1));
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
   bf162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
@@ -58,7 +65,7 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 // ============================================================================== forward
 template <int HD>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const Params p) {
   constexpr int NB = HD / 64;                 // 64-column blocks per head-dim
@@ -82,6 +89,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t* p_full = bars + 9;       // 1
   uint64_t* o_full = bars + 10;      // 1
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 11);
+  float* mx_ex = reinterpret_cast<float*>(bars + 16);   // [2 tiles][2 warpgroups][128 rows] row-max exchange
+  float* l_ex = mx_ex + 512;                            // [2 warpgroups][128 rows] row-sum exchange
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qi = (int)gridDim.x - 1 - (int)blockIdx.x;   // heaviest (last) query tiles first
@@ -103,9 +112,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc::mbar_init(&kv_full[s], 1);
       tc::mbar_init(&kv_empty[s], 1);
       tc::mbar_init(&s_full[s], 1);
-      tc::mbar_init(&s_free[s], 128);
+      tc::mbar_init(&s_free[s], 256);
     }
-    tc::mbar_init(p_full, 128);
+    tc::mbar_init(p_full, 256);
     tc::mbar_init(o_full, 1);
     tc::fence_barrier_init();
   }
@@ -172,15 +181,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
   } else {
-    // ------------------------------ softmax / accumulate / epilogue: one thread per query row
+    // ------------------------------ softmax / accumulate / epilogue
+    // Two warpgroups share every query row: thread (wg, r) owns key columns [64 wg, 64 wg + 64) of each
+    // S tile and output columns [wg HD/2, (wg+1) HD/2).  Two warps per scheduler hide each other's FFMA /
+    // MUFU latency; the row max is exchanged through shared memory once per tile, the row sum only at
+    // the end (both halves rescale with the same running max).
+    const int wg = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;
     const int q_idx = q0 + r;
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     const float scale2 = p.scale * kLog2e;
-    float acc[HD];
+    constexpr int OC = HD / 2;
+    float acc[OC];
 #pragma unroll
-    for (int i = 0; i < HD; ++i) acc[i] = 0.f;
+    for (int i = 0; i < OC; ++i) acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
 
     for (int j = 0; j < n_tiles; ++j) {
@@ -188,85 +203,93 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const int buf = j & 1;
       tc::mbar_wait(&s_full[buf], (j >> 1) & 1);
       tc::tc_fence_after();
-      const uint32_t tS = tmem_S + lane_off + buf * 128;
+      uint32_t v[64];
+      const uint32_t tS = tmem_S + lane_off + buf * 128 + wg * 64;
+      tc::tmem_ld_32x32(tS, v);
+      tc::tmem_ld_32x32(tS + 32, v + 32);
+      tc::tmem_ld_wait();
+      tc::tc_fence_before();
+      tc::mbar_arrive(&s_free[buf]);          // S lives in registers now: the MMA warp may refill this buffer
       const bool need_mask = (p.causal && (kv0 + BKV - 1 > q0)) || (kv0 + BKV > len);
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        uint32_t v[32];
-        tc::tmem_ld_32x32(tS + ch * 32, v);
-        tc::tmem_ld_wait();
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) {
-          float s = __uint_as_float(v[jj]);
-          if (need_mask) {
-            const int c = kv0 + ch * 32 + jj;
-            if (c >= len || (p.causal && c > q_idx)) s = -INFINITY;
-          }
-          mx = fmaxf(mx, s);
-        }
+      int limit = 64;                          // number of valid columns among my 64
+      if (need_mask) {
+        int lim = len;
+        if (p.causal) lim = min(lim, q_idx + 1);
+        limit = lim - (kv0 + wg * 64);
       }
+      float mx = -INFINITY;
+      if (!need_mask) {
+#pragma unroll
+        for (int jj = 0; jj < 64; ++jj) mx = fmaxf(mx, __uint_as_float(v[jj]));
+      } else {
+#pragma unroll
+        for (int jj = 0; jj < 64; ++jj) mx = fmaxf(mx, jj < limit ? __uint_as_float(v[jj]) : -INFINITY);
+      }
+      float* ex = mx_ex + (j & 1) * 256;
+      ex[wg * 128 + r] = mx;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      mx = fmaxf(mx, ex[(wg ^ 1) * 128 + r]);
       const float m_new = fmaxf(m_run, mx * scale2);
       const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
-      const float alpha = exp2f(m_run - m_use);
+      const float alpha = ex2_approx(m_run - m_use);
+      const float neg_m = -m_use;
       float sum = 0.f;
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
-        uint32_t v[32];
-        tc::tmem_ld_32x32(tS + ch * 32, v);
-        tc::tmem_ld_wait();
-        uint32_t pk[16];
+      uint32_t pk[32];
+      if (!need_mask) {
 #pragma unroll
-        for (int jj = 0; jj < 32; jj += 2) {
-          float p0 = exp2f(__uint_as_float(v[jj]) * scale2 - m_use);
-          float p1 = exp2f(__uint_as_float(v[jj + 1]) * scale2 - m_use);
-          if (need_mask) {
-            const int c = kv0 + ch * 32 + jj;
-            if (c >= len || (p.causal && c > q_idx)) p0 = 0.f;
-            if (c + 1 >= len || (p.causal && c + 1 > q_idx)) p1 = 0.f;
-          }
+        for (int jj = 0; jj < 64; jj += 2) {
+          const float p0 = ex2_approx(fmaf(__uint_as_float(v[jj]), scale2, neg_m));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(v[jj + 1]), scale2, neg_m));
           sum += p0 + p1;
           pk[jj >> 1] = pack_bf16x2(p0, p1);
         }
+      } else {
 #pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          const uint32_t off = sw128_offset(r, ch * 32 + q4 * 8);
-          *reinterpret_cast<uint4*>(sP + off) = make_uint4(pk[q4 * 4], pk[q4 * 4 + 1], pk[q4 * 4 + 2], pk[q4 * 4 + 3]);
+        for (int jj = 0; jj < 64; jj += 2) {
+          const float p0 = jj < limit ? ex2_approx(fmaf(__uint_as_float(v[jj]), scale2, neg_m)) : 0.f;
+          const float p1 = jj + 1 < limit ? ex2_approx(fmaf(__uint_as_float(v[jj + 1]), scale2, neg_m)) : 0.f;
+          sum += p0 + p1;
+          pk[jj >> 1] = pack_bf16x2(p0, p1);
         }
       }
+      uint8_t* prow = sP + wg * 16384 + r * 128;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        *reinterpret_cast<uint4*>(prow + ((c ^ (r & 7)) << 4)) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
       l_run = l_run * alpha + sum;
       m_run = m_new;
-      tc::tc_fence_before();
-      tc::mbar_arrive(&s_free[buf]);
       tc::fence_proxy_async();
       tc::mbar_arrive(p_full);
       // fold this tile's P V into the running output
       tc::mbar_wait(o_full, j & 1);
       tc::tc_fence_after();
 #pragma unroll
-      for (int ch = 0; ch < HD / 32; ++ch) {
-        uint32_t v[32];
-        tc::tmem_ld_32x32(tmem_O + lane_off + ch * 32, v);
+      for (int ch = 0; ch < OC / 32; ++ch) {
+        uint32_t o[32];
+        tc::tmem_ld_32x32(tmem_O + lane_off + wg * OC + ch * 32, o);
         tc::tmem_ld_wait();
 #pragma unroll
-        for (int jj = 0; jj < 32; ++jj) acc[ch * 32 + jj] = acc[ch * 32 + jj] * alpha + __uint_as_float(v[jj]);
+        for (int jj = 0; jj < 32; ++jj) acc[ch * 32 + jj] = fmaf(acc[ch * 32 + jj], alpha, __uint_as_float(o[jj]));
       }
       tc::tc_fence_before();
     }
-    // epilogue
+    // epilogue: combine the two halves' row sums, normalise, store
+    l_ex[wg * 128 + r] = l_run;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    const float l_tot = l_ex[r] + l_ex[128 + r];
     if (q_idx < p.T) {
-      const bool valid = (q_idx < len) && (l_run > 0.f);
-      const float inv = valid ? 1.f / l_run : 0.f;
-      bf16* dst = p.o + (int64_t)b * p.o_sb + (int64_t)q_idx * p.o_st + (int64_t)h * p.o_sh;
+      const bool valid = (q_idx < len) && (l_tot > 0.f);
+      const float inv = valid ? 1.f / l_tot : 0.f;
+      bf16* dst = p.o + (int64_t)b * p.o_sb + (int64_t)q_idx * p.o_st + (int64_t)h * p.o_sh + wg * OC;
 #pragma unroll
-      for (int c = 0; c < HD; c += 8) {
+      for (int c = 0; c < OC; c += 8) {
         float f[8];
 #pragma unroll
         for (int t = 0; t < 8; ++t) f[t] = acc[c + t] * inv;
         st8(dst + c, pack8(f));
       }
-      if (p.lse != nullptr)
-        p.lse[((int64_t)b * p.Hq + h) * p.T + q_idx] = valid ? (m_run + log2f(l_run)) * kLn2 : 0.f;
+      if (p.lse != nullptr && wg == 0)
+        p.lse[((int64_t)b * p.Hq + h) * p.T + q_idx] = valid ? (m_run + log2f(l_tot)) * kLn2 : 0.f;
     }
   }
   tc::tc_fence_before();
@@ -658,15 +681,15 @@ int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
   dim3 grid((T + BQ - 1) / BQ, Hq, B);
   cudaStream_t s = (cudaStream_t)stream;
   if (D == 128) {
-    constexpr int smem = 128 * 128 * 2 + 2 * 2 * 128 * 128 * 2 + 128 * 128 * 2 + 1024 + 256;
+    constexpr int smem = 128 * 128 * 2 + 2 * 2 * 128 * 128 * 2 + 128 * 128 * 2 + 1024 + 4096;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
-    attn_fwd_kernel<128><<<grid, kThreads, smem, s>>>(tmQ, tmK, tmV, p);
+    attn_fwd_kernel<128><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, p);
   } else {
-    constexpr int smem = 128 * 64 * 2 + 2 * 2 * 128 * 64 * 2 + 128 * 128 * 2 + 1024 + 256;
+    constexpr int smem = 128 * 64 * 2 + 2 * 2 * 128 * 64 * 2 + 128 * 128 * 2 + 1024 + 4096;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
-    attn_fwd_kernel<64><<<grid, kThreads, smem, s>>>(tmQ, tmK, tmV, p);
+    attn_fwd_kernel<64><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, p);
   }
   return check_launch("attn_fwd");
 }
