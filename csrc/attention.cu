@@ -22,8 +22,7 @@ namespace attn {
 
 constexpr int BQ = 128;
 constexpr int BKV = 128;
-constexpr int kThreads = 192;        // backward: TMA warp, MMA warp, 4 row-owner warps
-constexpr int kFwdThreads = 320;     // forward: TMA warp, MMA warp, 2 x 4 softmax warps
+constexpr int kFwdThreads = 320;     // TMA warp, MMA warp, 2 x 4 softmax / row-owner warps (forward and backward)
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -348,7 +347,7 @@ __global__ void attn_bwd_dq_cast_kernel(const float* __restrict__ dq_acc, bf16* 
 
 // ============================================================================== backward main
 template <int HD>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kFwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO, const Params p) {
   constexpr int NB = HD / 64;
@@ -393,8 +392,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     tc::mbar_init(qdo_full, 1);
     tc::mbar_init(qdo_empty, 1);
     tc::mbar_init(sdp_full, 1);
-    tc::mbar_init(sdp_free, 128);
-    tc::mbar_init(pds_full, 128);
+    tc::mbar_init(sdp_free, 256);
+    tc::mbar_init(pds_full, 256);
     tc::mbar_init(dq_full, 1);
     tc::fence_barrier_init();
   }
@@ -474,64 +473,84 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
   } else {
+    // Row-owner threads, two warpgroups per row: thread (wg, r) handles key columns [64 wg, 64 wg + 64) of
+    // S / dP (-> P, dS in shared memory) and columns [wg HD/2, (wg+1) HD/2) of dQ, dK, dV.
+    const int wg = (warp - 2) >> 2;
     const int quarter = warp & 3;
     const int r = quarter * 32 + lane;
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     const float scale2 = p.scale * kLog2e;
+    constexpr int OC = HD / 2;
     for (int it = 0; it < n_iters; ++it) {
       const int g = it / iters_per_head, i = i_begin + it % iters_per_head;
       const int h = hk * G + g;
       const int q0 = i * BQ;
       const int q_idx = q0 + r;
       const bool row_valid = q_idx < len;
-      float lse2 = 0.f, dlt = 0.f;
+      float neg_lse2 = 0.f, dlt = 0.f;
       if (row_valid) {
         const int64_t o = ((int64_t)b * p.Hq + h) * p.T + q_idx;
-        lse2 = p.lse[o] * kLog2e;
+        neg_lse2 = -p.lse[o] * kLog2e;
         dlt = p.delta[o];
       }
       const bool need_mask = (p.causal && (kv0 + BKV - 1 > q0)) || (kv0 + BKV > len) || (q0 + BQ > len);
+      int limit = 64;
+      if (need_mask) {
+        int lim = len;
+        if (p.causal) lim = min(lim, q_idx + 1);
+        limit = row_valid ? lim - (kv0 + wg * 64) : 0;
+      }
       tc::mbar_wait(sdp_full, it & 1);
       tc::tc_fence_after();
-#pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      uint8_t* prow = sP + wg * 16384 + r * 128;
+      uint8_t* drow = sdS + wg * 16384 + r * 128;
+#pragma unroll
+      for (int ch = 0; ch < 2; ++ch) {
         uint32_t s[32], dp[32];
-        tc::tmem_ld_32x32(tmem_S + lane_off + ch * 32, s);
-        tc::tmem_ld_32x32(tmem_dP + lane_off + ch * 32, dp);
+        tc::tmem_ld_32x32(tmem_S + lane_off + wg * 64 + ch * 32, s);
+        tc::tmem_ld_32x32(tmem_dP + lane_off + wg * 64 + ch * 32, dp);
         tc::tmem_ld_wait();
         uint32_t pk[16], dk_[16];
+        if (!need_mask) {
 #pragma unroll
-        for (int jj = 0; jj < 32; jj += 2) {
-          float p0 = exp2f(__uint_as_float(s[jj]) * scale2 - lse2);
-          float p1 = exp2f(__uint_as_float(s[jj + 1]) * scale2 - lse2);
-          if (need_mask) {
-            const int c = kv0 + ch * 32 + jj;
-            if (!row_valid || c >= len || (p.causal && c > q_idx)) p0 = 0.f;
-            if (!row_valid || c + 1 >= len || (p.causal && c + 1 > q_idx)) p1 = 0.f;
+          for (int jj = 0; jj < 32; jj += 2) {
+            const float p0 = ex2_approx(fmaf(__uint_as_float(s[jj]), scale2, neg_lse2));
+            const float p1 = ex2_approx(fmaf(__uint_as_float(s[jj + 1]), scale2, neg_lse2));
+            const float d0 = p0 * (__uint_as_float(dp[jj]) - dlt) * p.scale;
+            const float d1 = p1 * (__uint_as_float(dp[jj + 1]) - dlt) * p.scale;
+            pk[jj >> 1] = pack_bf16x2(p0, p1);
+            dk_[jj >> 1] = pack_bf16x2(d0, d1);
           }
-          const float d0 = p0 * (__uint_as_float(dp[jj]) - dlt) * p.scale;
-          const float d1 = p1 * (__uint_as_float(dp[jj + 1]) - dlt) * p.scale;
-          pk[jj >> 1] = pack_bf16x2(p0, p1);
-          dk_[jj >> 1] = pack_bf16x2(d0, d1);
+        } else {
+#pragma unroll
+          for (int jj = 0; jj < 32; jj += 2) {
+            const int e = ch * 32 + jj;
+            const float p0 = e < limit ? ex2_approx(fmaf(__uint_as_float(s[jj]), scale2, neg_lse2)) : 0.f;
+            const float p1 = e + 1 < limit ? ex2_approx(fmaf(__uint_as_float(s[jj + 1]), scale2, neg_lse2)) : 0.f;
+            const float d0 = p0 * (__uint_as_float(dp[jj]) - dlt) * p.scale;
+            const float d1 = p1 * (__uint_as_float(dp[jj + 1]) - dlt) * p.scale;
+            pk[jj >> 1] = pack_bf16x2(p0, p1);
+            dk_[jj >> 1] = pack_bf16x2(d0, d1);
+          }
         }
 #pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4) {
-          const uint32_t off = sw128_offset(r, ch * 32 + q4 * 8);
-          *reinterpret_cast<uint4*>(sP + off) = make_uint4(pk[q4 * 4], pk[q4 * 4 + 1], pk[q4 * 4 + 2], pk[q4 * 4 + 3]);
-          *reinterpret_cast<uint4*>(sdS + off) = make_uint4(dk_[q4 * 4], dk_[q4 * 4 + 1], dk_[q4 * 4 + 2], dk_[q4 * 4 + 3]);
+        for (int c = 0; c < 4; ++c) {
+          const int off = (((ch * 4 + c) ^ (r & 7)) << 4);
+          *reinterpret_cast<uint4*>(prow + off) = make_uint4(pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+          *reinterpret_cast<uint4*>(drow + off) = make_uint4(dk_[4 * c], dk_[4 * c + 1], dk_[4 * c + 2], dk_[4 * c + 3]);
         }
       }
       tc::tc_fence_before();
       tc::fence_proxy_async();
       tc::mbar_arrive(pds_full);
-      // dQ tile -> fp32 accumulator in global memory
+      // dQ tile -> fp32 accumulator in global memory (my half of the head dimension)
       tc::mbar_wait(dq_full, it & 1);
       tc::tc_fence_after();
-      float* dst = p.dq_acc + (((int64_t)b * p.T + q_idx) * p.Hq + h) * HD;
-#pragma unroll 1
-      for (int ch = 0; ch < HD / 32; ++ch) {
+      float* dst = p.dq_acc + (((int64_t)b * p.T + q_idx) * p.Hq + h) * HD + wg * OC;
+#pragma unroll
+      for (int ch = 0; ch < OC / 32; ++ch) {
         uint32_t v[32];
-        tc::tmem_ld_32x32(tmem_S + lane_off + ch * 32, v);
+        tc::tmem_ld_32x32(tmem_S + lane_off + wg * OC + ch * 32, v);
         tc::tmem_ld_wait();
         if (row_valid) {
 #pragma unroll
@@ -543,30 +562,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
     // dK / dV of this tile
     const int kv_idx = kv0 + r;
-    if (kv_idx < p.T) {
-      bf16* pdk = p.dk + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh;
-      bf16* pdv = p.dv + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh;
-      if (n_iters == 0) {
+    bf16* pdk = p.dk + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh + wg * OC;
+    bf16* pdv = p.dv + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh + wg * OC;
+    if (n_iters == 0) {
+      if (kv_idx < p.T) {
         const float zf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const bf16x8 z = pack8(zf);
 #pragma unroll
-        for (int c = 0; c < HD; c += 8) {
+        for (int c = 0; c < OC; c += 8) {
           st8(pdk + c, z);
           st8(pdv + c, z);
         }
       }
-    }
-    if (n_iters > 0) {
+    } else {
       // the last dq_full wait above already ordered every MMA (commits complete in issue order)
-#pragma unroll 1
-      for (int ch = 0; ch < HD / 32; ++ch) {
+#pragma unroll
+      for (int ch = 0; ch < OC / 32; ++ch) {
         uint32_t v[32], u[32];
-        tc::tmem_ld_32x32(tmem_dV + lane_off + ch * 32, v);
-        tc::tmem_ld_32x32(tmem_dK + lane_off + ch * 32, u);
+        tc::tmem_ld_32x32(tmem_dV + lane_off + wg * OC + ch * 32, v);
+        tc::tmem_ld_32x32(tmem_dK + lane_off + wg * OC + ch * 32, u);
         tc::tmem_ld_wait();
         if (kv_idx < p.T) {
-          bf16* pdk = p.dk + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh + ch * 32;
-          bf16* pdv = p.dv + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh + ch * 32;
 #pragma unroll
           for (int c = 0; c < 32; c += 8) {
             float f[8], e[8];
@@ -575,8 +591,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
               f[t] = __uint_as_float(v[c + t]);
               e[t] = __uint_as_float(u[c + t]);
             }
-            st8(pdv + c, pack8(f));
-            st8(pdk + c, pack8(e));
+            st8(pdv + ch * 32 + c, pack8(f));
+            st8(pdk + ch * 32 + c, pack8(e));
           }
         }
       }
@@ -722,12 +738,12 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
     constexpr int smem = 4 * 128 * 128 * 2 + 2 * 128 * 128 * 2 + 1024 + 256;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
-    attn_bwd_kernel<128><<<grid, kThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, p);
+    attn_bwd_kernel<128><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, p);
   } else {
     constexpr int smem = 4 * 128 * 64 * 2 + 2 * 128 * 128 * 2 + 1024 + 256;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
-    attn_bwd_kernel<64><<<grid, kThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, p);
+    attn_bwd_kernel<64><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, p);
   }
   if ((rc = check_launch("attn_bwd"))) return rc;
   int64_t blocks = (rows * (D / 8) + 255) / 256;

@@ -57,6 +57,22 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_
   return 0;
 }
 
+int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, int esize, uint64_t dim0, uint64_t dim1,
+                 uint64_t ld_elems, uint32_t box0, uint32_t box1) {
+  PFN_encodeTiled fn = get_encode_fn();
+  DLA_REQUIRE(fn != nullptr, DLA_E_DRIVER, "cuTensorMapEncodeTiled entry point not available");
+  DLA_REQUIRE(((uintptr_t)base & 15) == 0 && (ld_elems * esize) % 16 == 0, DLA_E_BADARG, "tensor map: unaligned base or pitch");
+  cuuint64_t dims[2] = {dim0, dim1};
+  cuuint64_t strides[1] = {ld_elems * (uint64_t)esize};
+  cuuint32_t box[2] = {box0, box1};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, dtype, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DLA_REQUIRE(r == CUDA_SUCCESS, DLA_E_DRIVER, "cuTensorMapEncodeTiled failed with %d (dims %llu x %llu, ld %llu, box %u x %u)",
+              (int)r, (unsigned long long)dim0, (unsigned long long)dim1, (unsigned long long)ld_elems, box0, box1);
+  return 0;
+}
+
 int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_elems[3],
                       const uint32_t box[4]) {
   PFN_encodeTiled fn = get_encode_fn();
@@ -90,7 +106,8 @@ constexpr int B_BYTES = BN * BK * 2;   // 32 KiB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int kThreads = 192;
 constexpr int kEpiWarps = 4;
-constexpr int SMEM_BYTES = kStages * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int EPI_BYTES = kEpiWarps * 2 * 4096;
+constexpr int SMEM_BYTES = kStages * STAGE_BYTES + EPI_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
 constexpr int GROUP_M = 16;
 
 enum Epi { kStore = 0, kLogprob = 1 };
@@ -100,12 +117,18 @@ struct Params {
   void* C;
   int64_t ldc;
   int c_fp32, accumulate;
+  int store_mode;     // 0 = TMA store / reduce-add through staged smem, 1 = direct st.global from the TMEM layout
   int num_m_tiles, num_n_tiles;
   // log-prob epilogue
   const int64_t* labels;
   float2* partials;   // [num_n_tiles, M] (max, sumexp)
   float* picked;      // [M] logit at the label
 };
+
+__device__ __forceinline__ uint32_t pack2(uint32_t a, uint32_t b) {
+  bf162 v = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b));
+  return *reinterpret_cast<uint32_t*>(&v);
+}
 
 __device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int& m_blk, int& n_blk) {
   const int per_group = GROUP_M * num_n;
@@ -119,10 +142,12 @@ __device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int& m_
 
 template <bool kAMN, bool kBMN, int kEpi>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Params p) {
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmC, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * STAGE_BYTES);
+  uint8_t* epi_smem = smem + kStages * STAGE_BYTES;              // 4 epilogue warps x 2 x 4 KiB staging
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_smem + EPI_BYTES);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -233,6 +258,54 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
 
       if constexpr (kEpi == kStore) {
+       if (p.store_mode == 0) {
+        // TMEM -> registers -> 128B-swizzled staging rows -> TMA store (or TMA reduce-add when accumulating).
+        // The output never touches the LSU path: uncoalesced per-row st.global from the TMEM layout used
+        // to eat ~45% of the L1TEX data pipe, which the tensor core shares for its operand reads.
+        const int gc = p.c_fp32 ? 32 : 64;                 // output columns per 128-byte staging row
+        const int n_groups = BN / gc;
+        uint8_t* stage_base = epi_smem + (warp - 2) * 2 * 4096;
+        const int r0 = m_blk * BM + quarter * 32;
+#pragma unroll 1
+        for (int gi = 0; gi < n_groups; ++gi) {
+          uint8_t* buf = stage_base + (gi & 1) * 4096;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // store from 2 groups ago read `buf`
+          __syncwarp();
+          uint8_t* myrow = buf + lane * 128;
+          if (p.c_fp32) {
+            uint32_t r[32];
+            tc::tmem_ld_32x32(taddr + gi * 32, r);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+              *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = make_uint4(r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+          } else {
+            uint32_t r[64];
+            tc::tmem_ld_32x32(taddr + gi * 64, r);
+            tc::tmem_ld_32x32(taddr + gi * 64 + 32, r + 32);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+              uint4 v;
+              v.x = pack2(r[8 * c], r[8 * c + 1]);
+              v.y = pack2(r[8 * c + 2], r[8 * c + 3]);
+              v.z = pack2(r[8 * c + 4], r[8 * c + 5]);
+              v.w = pack2(r[8 * c + 6], r[8 * c + 7]);
+              *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = v;
+            }
+          }
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            const int c0 = col_base + gi * gc;
+            if (c0 < p.N && r0 < p.M) {       // TMA clips the box at the tensor bounds
+              if (p.accumulate) tc::tma_reduce_add_2d(&tmC, buf, c0, r0);
+              else tc::tma_store_2d(&tmC, buf, c0, r0);
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
+       } else {
 #pragma unroll 1
         for (int ch = 0; ch < BN / 32; ++ch) {
           uint32_t r[32];
@@ -283,6 +356,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
         }
+       }
       } else {
         // ---- fused log-softmax partials: (max, sum exp(x - max)) of this row over the tile's columns
         constexpr float kLog2e = 1.4426950408889634f;
@@ -330,6 +404,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   }
 
+  if (kEpi == kStore && warp >= 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -387,7 +462,7 @@ logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, co
 static int g_variant = 0;
 
 template <bool kAMN, bool kBMN, int kEpi>
-static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& p, cudaStream_t stream) {
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
   auto kern = gemm_kernel<kAMN, kBMN, kEpi>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -396,7 +471,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const Params& 
   }
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
-  kern<<<grid, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, p);
+  kern<<<grid, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);
   return check_launch("gemm_bf16");
 }
 
@@ -438,11 +513,20 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   p.M = M; p.N = N; p.K = K; p.C = C; p.ldc = ldc; p.c_fp32 = c_fp32; p.accumulate = accumulate;
   p.num_m_tiles = (M + BM - 1) / BM;
   p.num_n_tiles = (N + BN - 1) / BN;
+  const int64_t esz = c_fp32 ? 4 : 2;
+  const bool tma_ok = (((uintptr_t)C & 15) == 0) && ((ldc * esz) % 16 == 0) && g_variant != 1;
+  p.store_mode = tma_ok ? 0 : 1;
+  CUtensorMap tmC{};
+  if (tma_ok) {
+    rc = make_tmap_2d(&tmC, C, c_fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (int)esz, (uint64_t)N,
+                      (uint64_t)M, (uint64_t)ldc, c_fp32 ? 32 : 64, 32);
+    if (rc) return rc;
+  }
   cudaStream_t s = (cudaStream_t)stream;
-  if (!a_mn_major && !b_mn_major) return launch<false, false, kStore>(tmA, tmB, p, s);
-  if (!a_mn_major && b_mn_major) return launch<false, true, kStore>(tmA, tmB, p, s);
-  if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, p, s);
-  return launch<true, true, kStore>(tmA, tmB, p, s);
+  if (!a_mn_major && !b_mn_major) return launch<false, false, kStore>(tmA, tmB, tmC, p, s);
+  if (!a_mn_major && b_mn_major) return launch<false, true, kStore>(tmA, tmB, tmC, p, s);
+  if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, tmC, p, s);
+  return launch<true, true, kStore>(tmA, tmB, tmC, p, s);
 }
 
 size_t dla_lmhead_scratch_bytes(int M, int V) {
@@ -466,7 +550,7 @@ int dla_lmhead_logprob(const void* X, const void* W, const int64_t* labels, int 
   p.partials = reinterpret_cast<float2*>(scratch);
   p.picked = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + (size_t)p.num_n_tiles * M * sizeof(float2));
   cudaStream_t s = (cudaStream_t)stream;
-  rc = launch<false, false, kLogprob>(tmA, tmB, p, s);
+  rc = launch<false, false, kLogprob>(tmA, tmB, CUtensorMap{}, p, s);
   if (rc) return rc;
   logprob_combine_kernel<<<(M + 255) / 256, 256, 0, s>>>(p.partials, p.picked, labels, M, p.num_n_tiles, logp, lse);
   return check_launch("lmhead_logprob.combine");
@@ -575,7 +659,7 @@ int dla_lmhead_logprob_noalloc(const void* X, const void* W, const int64_t* labe
   p.labels = labels;
   p.partials = area->partials;     // [n_tiles, M] packed with pitch M, exactly like the caller-scratch path
   p.picked = area->picked;
-  rc = launch<false, false, kLogprob>(tmA, tmB, p, s);
+  rc = launch<false, false, kLogprob>(tmA, tmB, CUtensorMap{}, p, s);
   if (rc) return rc;
   logprob_combine_kernel<<<(M + 255) / 256, 256, 0, s>>>(p.partials, p.picked, labels, M, p.num_n_tiles, logp, lse);
   return check_launch("lmhead_logprob_noalloc.combine");

@@ -81,6 +81,21 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
       : "memory");
 }
 
+// 2D tile store shared -> global (bulk-group completion); the box is clipped at the tensor bounds
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+// 2D tile reduce-add shared -> global: global[tile] += smem[tile], done by the memory system (element type
+// comes from the tensor map)
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+
 // 4D tile load (coordinates innermost first)
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
   asm volatile(
@@ -217,6 +232,8 @@ __device__ __forceinline__ void cluster_sync() {
 // (box0, box1), SWIZZLE_128B (box0 * 2 bytes must be <= 128).
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_t dim1, uint64_t ld_elems,
                       uint32_t box0, uint32_t box1);
+int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, int esize, uint64_t dim0, uint64_t dim1,
+                 uint64_t ld_elems, uint32_t box0, uint32_t box1);
 // Rank-4 bf16 map: dims[0] contiguous; strides_elems[i] is the pitch of dims[i+1] in elements.
 int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_elems[3],
                       const uint32_t box[4]);

@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""Per-kernel time breakdown of ONE Llama-3-8B DPO step (CUPTI via torch.profiler; numbers taken under the
+profiler are for SHARES only, never bench values).  Writes gpurun_out/step_breakdown.json."""
+import json
+import os
+import sys
+from collections import defaultdict
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+os.environ.setdefault("PYTORCH_CUDA_ALLOC_CONF", "expandable_segments:True")
+
+from dla_b200.algo import dpo_step  # noqa: E402
+from dla_b200.data.synthetic import synthetic_preference_batch  # noqa: E402
+from dla_b200.models.factory import load_causal_lm  # noqa: E402
+from dla_b200.optim import AdamWConfig  # noqa: E402
+from dla_b200.parallel.pg import init_distributed  # noqa: E402
+
+model = sys.argv[1] if len(sys.argv) > 1 else "llama3-8b"
+ctx = init_distributed()
+policy = load_causal_lm(model, ctx, gradient_checkpointing=True, name="policy")
+ref = load_causal_lm(model, ctx, gradient_checkpointing=False, trainable=False, name="reference")
+opt = AdamWConfig(lr=1e-6, weight_decay=0.01)
+batch = synthetic_preference_batch(4, 1024, policy.config.vocab_size, seed=0)
+batch = {s: {k: v.cuda() for k, v in batch[s].items()} for s in batch}
+
+
+def step():
+    loss, _ = dpo_step(policy.model, ref.model, batch, beta=0.1)
+    loss.backward()
+    policy.engine.finish_backward()
+    policy.engine.optimizer_step(opt)
+
+
+for _ in range(2):
+    step()
+torch.cuda.synchronize()
+with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) as prof:
+    step()
+    torch.cuda.synchronize()
+agg = defaultdict(lambda: [0.0, 0])
+for ev in prof.events():
+    if ev.device_type == torch.autograd.DeviceType.CUDA:
+        name = ev.name
+        for key in ("gemm_kernel", "attn_fwd", "attn_bwd_kernel", "attn_bwd_prep", "attn_bwd_dq", "rmsnorm_fwd", "rmsnorm_bwd",
+                    "colsum", "rope", "swiglu_fwd", "swiglu_bwd", "adamw", "sumsq", "embedding", "logprob_grad", "logprob_combine",
+                    "Memset", "Memcpy", "elementwise", "fill", "copy"):
+            if key in name:
+                if key == "gemm_kernel":
+                    key = "gemm_logprob" if "ELi1E" in name or ", 1>" in name or "(int)1>" in name else "gemm_store"
+                name = key
+                break
+        agg[name][0] += ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
+        agg[name][1] += 1
+rows = sorted(((k, v[0] / 1e3, v[1]) for k, v in agg.items()), key=lambda r: -r[1])
+total = sum(r[1] for r in rows)
+print(f"total kernel time {total:.1f} ms")
+for k, ms, n in rows[:30]:
+    print(f"{ms:9.2f} ms {100 * ms / total:5.1f}%  x{n:5d}  {k[:100]}")
+Path(ROOT / "gpurun_out").mkdir(exist_ok=True)
+json.dump({"total_ms": total, "rows": rows[:40]}, open(ROOT / "gpurun_out" / "step_breakdown.json", "w"), indent=1)
