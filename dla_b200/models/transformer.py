@@ -139,6 +139,10 @@ class ParamProvider:
 
     trainable: bool = True
     checkpoint: bool = True
+    no_recompute: frozenset = frozenset()     # units that keep their activations instead of recomputing (HBM permitting)
+
+    def note_plain(self, unit: str) -> None:
+        pass
 
     def acquire(self, unit: str, backward: bool = False) -> Weights:  # pragma: no cover - interface
         raise NotImplementedError
@@ -281,13 +285,15 @@ def _anchor(device: torch.device) -> torch.Tensor:
 
 def run_unit(provider: ParamProvider, unit: str, fn: Callable, *inputs):
     grad_mode = torch.is_grad_enabled() and provider.trainable
-    if grad_mode and provider.checkpoint:
+    if grad_mode and provider.checkpoint and unit not in provider.no_recompute:
         dev = next(t.device for t in inputs if isinstance(t, torch.Tensor))
         return _CheckpointedUnit.apply(provider, unit, fn, _anchor(dev), *inputs)
     w = provider.acquire(unit, backward=False)
     out = fn(w, *inputs)
     if not grad_mode:
         provider.release(unit, backward=False)
+    else:
+        provider.note_plain(unit)       # activations stay alive for a plain autograd backward (no recompute)
     return out
 
 

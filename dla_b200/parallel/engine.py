@@ -97,6 +97,7 @@ class Engine(ParamProvider):
         self._reduce_work: List[Any] = []
         self._passes_expected = 1
         self._passes_seen: Dict[str, int] = {}
+        self._plain_used: set = set()
         self.sync_grads = True          # False on non-boundary accumulation micro-steps (``no_sync``)
         self.step_count = 0
         self._sumsq = None
@@ -159,6 +160,34 @@ class Engine(ParamProvider):
             self._sq_scratch = torch.empty(N.sumsq_blocks(), dtype=torch.float32, device=self.device)
 
     # ------------------------------------------------------------------ ParamProvider
+    def note_plain(self, unit: str) -> None:
+        self._plain_used.add(unit)
+
+    def set_no_recompute_layers(self, k: int) -> int:
+        """Keep the activations of the LAST ``k`` decoder layers instead of recomputing them in backward
+        (they are the first to be consumed, so their memory is released earliest).  Returns k."""
+        layers = [u.name for u in self.units if u.name.startswith("layer.")]
+        k = max(0, min(int(k), len(layers)))
+        self.no_recompute = frozenset(layers[len(layers) - k:]) if k else frozenset()
+        return k
+
+    def auto_no_recompute(self, tokens: int, reserve_gb: float = 10.0) -> int:
+        """Spend free HBM on skipping recomputation: per decoder layer a plain backward keeps roughly
+        ``tokens * (8 H + 2 qkv + 6 F)`` bytes of bf16 activations alive.  Call after a warm-up step."""
+        if self.device.type != "cuda" or not self.resident:
+            return 0
+        cfg = self.cfg
+        per_layer = tokens * (8 * cfg.hidden_size + 2 * (cfg.q_dim + 2 * cfg.kv_dim) + 2 * cfg.q_dim + 6 * cfg.intermediate_size)
+        torch.cuda.synchronize(self.device)
+        free, _ = torch.cuda.mem_get_info(self.device)
+        free += torch.cuda.memory_reserved(self.device) - torch.cuda.memory_allocated(self.device)
+        k = int(max(0, free - reserve_gb * (1 << 30)) // max(per_layer, 1))
+        if self.ctx.world_size > 1:     # every rank must take the same decision
+            t = torch.tensor([k], device=self.device)
+            dist.all_reduce(t, dist.ReduceOp.MIN, group=self.ctx.group)
+            k = int(t.item())
+        return self.set_no_recompute_layers(k)
+
     def expect_passes(self, k: int) -> None:
         """How many backward passes traverse each unit per micro-step (2 when chosen/rejected run as
         separate forwards like ``R/src/training/train_dpo.py:113-114``)."""
@@ -261,6 +290,10 @@ class Engine(ParamProvider):
         micro-step and folds reduce-scatter outputs into the shard accumulators."""
         for unit, w in list(self._views.items()):
             collect_autograd_grads(w)
+        for unit in sorted(self._plain_used):          # units that ran without recompute have no per-unit hook
+            self._passes_seen[unit] = self._passes_expected - 1
+            self.grads_done(unit, self._views.get(unit, {}))
+        self._plain_used.clear()
         self._drain(0)
         if self.fused and self.sync_grads:
             self.fc.barrier(0)      # every rank's gradient buckets are complete before anyone reads them

@@ -89,3 +89,24 @@ def test_dpo_concat_equals_separate_and_learns():
             pol.flat[u.name].data.add_(pol.grad[u.name], alpha=-0.5)
         losses.append(loss.item())
     assert losses[-1] < losses[0] - 0.1, losses
+
+
+def test_no_recompute_layers_give_same_gradients():
+    from dla_b200.models.config import ModelConfig
+    from dla_b200.parallel.engine import Engine
+    from dla_b200.parallel.pg import DistContext
+
+    cfg = resolve_model_config("tiny-llama")
+    units = build_units(cfg)
+    ctx = DistContext()
+    a = Engine(cfg, units, ctx, trainable=True, checkpoint=True, dtype=torch.float32, seed=2)
+    b = Engine(cfg, units, ctx, trainable=True, checkpoint=True, dtype=torch.float32, seed=2)
+    assert b.set_no_recompute_layers(1) == 1 and b.no_recompute == frozenset({"layer.1"})
+    batch = synthetic_lm_batch(2, 16, cfg.vocab_size, seed=4)
+    for eng in (a, b):
+        loss = sft_loss(CausalLM(cfg, eng), batch)
+        loss.backward()
+        eng.finish_backward()
+    for u in units:
+        assert torch.allclose(a.gradbuf[u.name], b.gradbuf[u.name], atol=1e-6), u.name
+        assert a.gradbuf[u.name].abs().sum() > 0
