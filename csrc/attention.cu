@@ -349,7 +349,8 @@ __global__ void attn_bwd_dq_cast_kernel(const float* __restrict__ dq_acc, bf16* 
 template <int HD>
 __global__ void __launch_bounds__(kFwdThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO, const Params p) {
+                const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                const __grid_constant__ CUtensorMap tmdQ, const Params p) {
   constexpr int NB = HD / 64;
   constexpr int T_BYTES = 128 * HD * 2;       // one [128 x HD] operand tile
   constexpr int P_BYTES = 128 * 128 * 2;
@@ -502,6 +503,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       tc::mbar_wait(sdp_full, it & 1);
       tc::tc_fence_after();
+      if (it > 0) {     // the previous iteration's dQ reduce must have finished READING the staging area
+        if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+      }
       uint8_t* prow = sP + wg * 16384 + r * 128;
       uint8_t* drow = sdS + wg * 16384 + r * 128;
 #pragma unroll
@@ -543,23 +548,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc::tc_fence_before();
       tc::fence_proxy_async();
       tc::mbar_arrive(pds_full);
-      // dQ tile -> fp32 accumulator in global memory (my half of the head dimension)
+      // dQ tile -> staged in shared memory (the P / dS buffers are idle once this iteration's MMAs retired)
+      // -> ONE bulk reduce-add per 32-column block into the fp32 accumulator.  Per-lane red.global.add was
+      // ~1 lane/clk/SM: 16 K atomics per iteration dominated the kernel.
       tc::mbar_wait(dq_full, it & 1);
       tc::tc_fence_after();
-      float* dst = p.dq_acc + (((int64_t)b * p.T + q_idx) * p.Hq + h) * HD + wg * OC;
 #pragma unroll
       for (int ch = 0; ch < OC / 32; ++ch) {
         uint32_t v[32];
         tc::tmem_ld_32x32(tmem_S + lane_off + wg * OC + ch * 32, v);
         tc::tmem_ld_wait();
-        if (row_valid) {
+        uint8_t* blk = sP + (wg * (OC / 32) + ch) * 16384 + r * 128;
 #pragma unroll
-          for (int jj = 0; jj < 32; ++jj) atomicAdd(dst + ch * 32 + jj, __uint_as_float(v[jj]));
-        }
+        for (int c = 0; c < 8; ++c)
+          *reinterpret_cast<uint4*>(blk + ((c ^ (r & 7)) << 4)) = make_uint4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
       }
       tc::tc_fence_before();
-      tc::mbar_arrive(sdp_free);
+      tc::mbar_arrive(sdp_free);               // TMEM S / dP may be overwritten by the next iteration's MMAs
+      tc::fence_proxy_async();
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      if (threadIdx.x == 64) {
+#pragma unroll
+        for (int blk = 0; blk < HD / 32; ++blk) tc::tma_reduce_add_4d(&tmdQ, sP + blk * 16384, blk * 32, h, q0, b);
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
     }
+    if (threadIdx.x == 64) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     // dK / dV of this tile
     const int kv_idx = kv0 + r;
     bf16* pdk = p.dk + (int64_t)b * p.dkv_sb + (int64_t)kv_idx * p.dkv_st + (int64_t)hk * p.dkv_sh + wg * OC;
@@ -723,6 +737,13 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   if ((rc = make_qkv_map(&tmK, k, B, T, Hk, D, kv_sb, kv_st, kv_sh))) return rc;
   if ((rc = make_qkv_map(&tmV, v, B, T, Hk, D, kv_sb, kv_st, kv_sh))) return rc;
   if ((rc = make_qkv_map(&tmdO, dout, B, T, Hq, D, o_sb, o_st, o_sh))) return rc;
+  CUtensorMap tmdQ;
+  {   // fp32 accumulator [B, T, Hq, D], contiguous
+    const uint64_t dims[4] = {(uint64_t)D, (uint64_t)Hq, (uint64_t)T, (uint64_t)B};
+    const uint64_t strides[3] = {(uint64_t)D, (uint64_t)Hq * D, (uint64_t)T * Hq * D};
+    const uint32_t box[4] = {32, 1, 128, 1};
+    if ((rc = make_tmap_4d(&tmdQ, dq_acc, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dims, strides, box))) return rc;
+  }
   cudaStream_t s = (cudaStream_t)stream;
   const int64_t rows = (int64_t)B * T * Hq;
   attn_bwd_prep_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, s>>>((const bf16*)o, (const bf16*)dout, delta, dq_acc, B, T, Hq, D,
@@ -738,12 +759,12 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
     constexpr int smem = 4 * 128 * 128 * 2 + 2 * 128 * 128 * 2 + 1024 + 256;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
-    attn_bwd_kernel<128><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, p);
+    attn_bwd_kernel<128><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, tmdQ, p);
   } else {
     constexpr int smem = 4 * 128 * 64 * 2 + 2 * 128 * 128 * 2 + 1024 + 256;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
-    attn_bwd_kernel<64><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, p);
+    attn_bwd_kernel<64><<<grid, kFwdThreads, smem, s>>>(tmQ, tmK, tmV, tmdO, tmdQ, p);
   }
   if ((rc = check_launch("attn_bwd"))) return rc;
   int64_t blocks = (rows * (D / 8) + 255) / 256;

@@ -75,6 +75,11 @@ int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, 
 
 int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_elems[3],
                       const uint32_t box[4]) {
+  return make_tmap_4d(out, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dims, strides_elems, box);
+}
+
+int make_tmap_4d(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, int esize, const uint64_t dims[4],
+                 const uint64_t strides_elems[3], const uint32_t box[4]) {
   PFN_encodeTiled fn = get_encode_fn();
   DLA_REQUIRE(fn != nullptr, DLA_E_DRIVER, "cuTensorMapEncodeTiled entry point not available");
   DLA_REQUIRE(((uintptr_t)base & 15) == 0, DLA_E_BADARG, "tensor map: base must be 16-byte aligned");
@@ -82,11 +87,11 @@ int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4]
   cuuint32_t bx[4], es[4] = {1, 1, 1, 1};
   for (int i = 0; i < 4; ++i) { d[i] = dims[i]; bx[i] = box[i]; }
   for (int i = 0; i < 3; ++i) {
-    st[i] = strides_elems[i] * 2;
+    st[i] = strides_elems[i] * (uint64_t)esize;
     DLA_REQUIRE(st[i] % 16 == 0, DLA_E_BADARG, "tensor map: stride %d (%llu elements) must be a multiple of 8 elements", i,
                 (unsigned long long)strides_elems[i]);
   }
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), d, st, bx, es,
+  CUresult r = fn(out, dtype, 4, const_cast<void*>(base), d, st, bx, es,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   DLA_REQUIRE(r == CUDA_SUCCESS, DLA_E_DRIVER, "cuTensorMapEncodeTiled(4d) failed with %d", (int)r);

@@ -96,6 +96,13 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const vo
                : "memory");
 }
 
+__device__ __forceinline__ void tma_reduce_add_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
 // 4D tile load (coordinates innermost first)
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
   asm volatile(
@@ -234,6 +241,8 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t dim0, uint64_
                       uint32_t box0, uint32_t box1);
 int make_tmap_2d(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, int esize, uint64_t dim0, uint64_t dim1,
                  uint64_t ld_elems, uint32_t box0, uint32_t box1);
+int make_tmap_4d(CUtensorMap* out, const void* base, CUtensorMapDataType dtype, int esize, const uint64_t dims[4],
+                 const uint64_t strides_elems[3], const uint32_t box[4]);
 // Rank-4 bf16 map: dims[0] contiguous; strides_elems[i] is the pitch of dims[i+1] in elements.
 int make_tmap_4d_bf16(CUtensorMap* out, const void* base, const uint64_t dims[4], const uint64_t strides_elems[3],
                       const uint32_t box[4]);
