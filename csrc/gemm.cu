@@ -128,6 +128,15 @@ struct Params {
   const int64_t* labels;
   float2* partials;   // [num_n_tiles, M] (max, sumexp)
   float* picked;      // [M] logit at the label
+  // all-gather fused mode (path (b)): B's rows live sharded across ranks inside a flat unit buffer; the
+  // first ag_ncopy CTAs pull them from the owners' memory over NVLink into `ag_full` tile by tile while the
+  // other CTAs run the GEMM, each B tile being consumed as soon as its flag is published
+  const bf16* const* ag_peers;   // [world] every rank's shard of the unit (ag_S elements each)
+  bf16* ag_full;                 // local gathered unit buffer (B = ag_full + ag_b_off)
+  int64_t ag_S, ag_b_off;
+  uint32_t* ag_flags;            // [num_n_tiles] epoch-stamped "tile is local" flags
+  uint32_t ag_epoch;
+  int ag_ncopy, ag_world, ag_rank;
 };
 
 __device__ __forceinline__ uint32_t pack2(uint32_t a, uint32_t b) {
@@ -145,6 +154,75 @@ __device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int& m_
   n_blk = r / gsz;
 }
 
+// AG mode: all m-tiles of one n-tile are consecutive, n-tiles start at this rank's own rows (already local)
+__device__ __forceinline__ void tile_coords_ag(int t, int num_m, int num_n, int first_n, int& m_blk, int& n_blk) {
+  m_blk = t % num_m;
+  n_blk = (t / num_m + first_n) % num_n;
+}
+
+__device__ __forceinline__ int ag_first_tile(const Params& p) {
+  // first n-tile whose rows start inside this rank's shard
+  const int64_t tile_elems = (int64_t)BN * p.K;
+  const int64_t my_lo = p.ag_S * p.ag_rank;
+  int64_t t = (my_lo - p.ag_b_off + tile_elems - 1) / tile_elems;
+  if (t < 0) t = 0;
+  return (int)(t % p.num_n_tiles);
+}
+
+// Copy role of the all-gather fused GEMM: one thread drives TMA bulk copies peer HBM -> smem -> local HBM
+// through a ring of 32 KiB buffers (several MB in flight chip-wide hides the ~2 us NVLink latency), then
+// publishes the tile's flag with release semantics.
+__device__ void ag_copy_role(const Params& p, uint8_t* smem, uint64_t* bars) {
+  constexpr int kBuf = 6, kPiece = 32768, kAhead = kBuf - 2;
+  if (threadIdx.x != 0) return;
+  for (int b = 0; b < kBuf; ++b) tc::mbar_init(&bars[b], 1);
+  tc::fence_barrier_init();
+  const int first_n = ag_first_tile(p);
+  const int64_t tile_elems = (int64_t)BN * p.K;
+  const int64_t b_total = (int64_t)p.N * p.K;
+  uint32_t phase_bits = 0;
+  long long issued = 0, stored = 0;
+  struct Piece { const bf16* src; bf16* dst; uint32_t bytes; };
+  Piece ring[kBuf];
+  for (int seq = blockIdx.x; seq < p.num_n_tiles; seq += p.ag_ncopy) {
+    const int n_blk = (seq + first_n) % p.num_n_tiles;
+    int64_t e = (int64_t)n_blk * tile_elems;                       // element offset inside B
+    const int64_t e_end = (e + tile_elems < b_total) ? e + tile_elems : b_total;
+    while (e < e_end || stored < issued) {
+      if (e < e_end && issued - stored < kAhead) {
+        const int64_t flat = p.ag_b_off + e;                       // offset inside the unit
+        const int owner = (int)(flat / p.ag_S);
+        const int64_t in_shard = flat - (int64_t)owner * p.ag_S;
+        int64_t n = e_end - e;
+        if (n > kPiece / 2) n = kPiece / 2;
+        if (n > p.ag_S - in_shard) n = p.ag_S - in_shard;                   // do not straddle an owner boundary
+        const int b = (int)(issued % kBuf);
+        if (issued >= kBuf) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // store of piece issued-kBuf drained
+        ring[b] = Piece{p.ag_peers[owner] + in_shard, p.ag_full + flat, (uint32_t)(n * 2)};
+        tc::mbar_expect_tx(&bars[b], ring[b].bytes);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         tc::smem_u32(smem + b * kPiece)),
+                     "l"(ring[b].src), "r"(ring[b].bytes), "r"(tc::smem_u32(&bars[b]))
+                     : "memory");
+        ++issued;
+        e += n;
+      } else {
+        const int b = (int)(stored % kBuf);
+        tc::mbar_wait(&bars[b], (phase_bits >> b) & 1u);
+        phase_bits ^= 1u << b;
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(ring[b].dst),
+                     "r"(tc::smem_u32(smem + b * kPiece)), "r"(ring[b].bytes)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        ++stored;
+      }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // the tile's bytes are in local HBM
+    __threadfence();
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.ag_flags + n_blk), "r"(p.ag_epoch) : "memory");
+  }
+}
+
 template <bool kAMN, bool kBMN, int kEpi>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -158,6 +236,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
+  const int n_copy = p.ag_ncopy;
+  if (n_copy > 0 && (int)blockIdx.x < n_copy) {      // lowest block ids are scheduled first: copies never starve
+    ag_copy_role(p, smem, full_bar);
+    return;
+  }
+  const int cta = (int)blockIdx.x - n_copy, n_cta = (int)gridDim.x - n_copy;
+  const int ag_first = n_copy > 0 ? ag_first_tile(p) : 0;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = (p.K + BK - 1) / BK;
@@ -187,9 +272,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = cta; t < num_tiles; t += n_cta) {
         int m_blk, n_blk;
-        tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+        if (n_copy > 0) {
+          tile_coords_ag(t, p.num_m_tiles, p.num_n_tiles, ag_first, m_blk, n_blk);
+          // wait until the copy CTAs have landed this B tile in local memory, then order the generic-proxy
+          // flag read before the async-proxy (TMA) reads of the tile
+          uint32_t seen;
+          do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.ag_flags + n_blk) : "memory");
+            if (seen != p.ag_epoch) __nanosleep(100);
+          } while (seen != p.ag_epoch);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        } else {
+          tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+        }
         const int m0 = m_blk * BM, n0 = n_blk * BN;
         for (int kb = 0; kb < num_kb; ++kb) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -220,7 +317,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+      for (int t = cta; t < num_tiles; t += n_cta, ++it) {
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -251,9 +348,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     // ===================== epilogue (warps 2..5) =====================
     const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
     int it = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+    for (int t = cta; t < num_tiles; t += n_cta, ++it) {
       int m_blk, n_blk;
-      tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+      if (n_copy > 0) tile_coords_ag(t, p.num_m_tiles, p.num_n_tiles, ag_first, m_blk, n_blk);
+      else tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       tc::mbar_wait(&tfull_bar[acc], acc_phase);
@@ -475,7 +573,8 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
     attr_set = true;
   }
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
-  const int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
+  int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
+  if (p.ag_ncopy > 0) grid = kNumSMs;     // copy + compute CTAs must all be co-resident (1 CTA / SM)
   kern<<<grid, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);
   return check_launch("gemm_bf16");
 }
@@ -532,6 +631,37 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   if (!a_mn_major && b_mn_major) return launch<false, true, kStore>(tmA, tmB, tmC, p, s);
   if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, tmC, p, s);
   return launch<true, true, kStore>(tmA, tmB, tmC, p, s);
+}
+
+int dla_ag_gemm_bf16(const void* A, const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t b_offset,
+                     void* C, int M, int N, int K, int64_t lda, int64_t ldc, int world, int rank, uint32_t* flags,
+                     uint32_t epoch, int n_copy_ctas, int c_fp32, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M > 0 && N > 0 && K > 0 && K % 8 == 0, DLA_E_BADARG, "ag_gemm: bad shape %dx%dx%d", M, N, K);
+  DLA_REQUIRE(world >= 1 && rank >= 0 && rank < world && shard_elems % 8 == 0 && b_offset % 8 == 0, DLA_E_BADARG,
+              "ag_gemm: bad world/rank/shard (%d/%d/%lld)", world, rank, (long long)shard_elems);
+  DLA_REQUIRE(b_offset + (int64_t)N * K <= shard_elems * world, DLA_E_BADARG, "ag_gemm: B exceeds the unit");
+  DLA_REQUIRE(n_copy_ctas >= 1 && n_copy_ctas <= 64 && flags != nullptr, DLA_E_BADARG, "ag_gemm: n_copy_ctas in [1,64] and flags required");
+  bf16* B = reinterpret_cast<bf16*>(unit_full) + b_offset;
+  CUtensorMap tmA, tmB;
+  int rc = build_maps(&tmA, &tmB, A, B, M, N, K, lda, K, 0, 0);
+  if (rc) return rc;
+  Params p{};
+  p.M = M; p.N = N; p.K = K; p.C = C; p.ldc = ldc; p.c_fp32 = c_fp32; p.accumulate = 0;
+  p.num_m_tiles = (M + BM - 1) / BM;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  const int64_t esz = c_fp32 ? 4 : 2;
+  DLA_REQUIRE((((uintptr_t)C & 15) == 0) && ((ldc * esz) % 16 == 0), DLA_E_BADARG, "ag_gemm: C must be 16-byte aligned with a 16-byte pitch");
+  p.store_mode = 0;
+  CUtensorMap tmC{};
+  rc = make_tmap_2d(&tmC, C, c_fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (int)esz, (uint64_t)N,
+                    (uint64_t)M, (uint64_t)ldc, c_fp32 ? 32 : 64, 32);
+  if (rc) return rc;
+  p.ag_peers = reinterpret_cast<const bf16* const*>(peer_shards);
+  p.ag_full = reinterpret_cast<bf16*>(unit_full);
+  p.ag_S = shard_elems; p.ag_b_off = b_offset; p.ag_flags = flags; p.ag_epoch = epoch;
+  p.ag_ncopy = n_copy_ctas; p.ag_world = world; p.ag_rank = rank;
+  return launch<false, false, kStore>(tmA, tmB, tmC, p, (cudaStream_t)stream);
 }
 
 size_t dla_lmhead_scratch_bytes(int M, int V) {

@@ -168,6 +168,18 @@ peer_push_kernel(const bf16* __restrict__ src, bf16* const* peers, int world, in
   }
 }
 
+// gather a flat range of a sharded unit: element e comes from rank e / S at offset e % S
+__global__ void __launch_bounds__(256)
+peer_gather_kernel(const bf16* const* peers, bf16* __restrict__ full, int64_t S, int64_t offset, int64_t n) {
+  const int64_t nvec = n >> 3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = offset + i * 8;
+    const int owner = (int)(e / S);
+    const uint4 u = ld_peer16(peers[owner] + (e - (int64_t)owner * S));
+    *reinterpret_cast<uint4*>(full + e) = u;
+  }
+}
+
 // ------------------------------------------------------------------------------- (c) gather + DPO loss
 __device__ __forceinline__ float log_sigmoid(float z) { return fminf(z, 0.f) - log1pf(__expf(-fabsf(z))); }
 __device__ __forceinline__ float sigmoid_(float z) { return 1.f / (1.f + __expf(-z)); }
@@ -298,6 +310,19 @@ int dla_peer_push(const void* src, void* const* peers, int world, int rank, int6
   if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
   peer_push_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)src, reinterpret_cast<bf16* const*>(peers), world, rank, dst_offset, n);
   return check_launch("peer_push");
+}
+
+int dla_peer_gather(const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t offset, int64_t n, int world,
+                    void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && shard_elems % 8 == 0 && offset % 8 == 0 && n % 8 == 0, DLA_E_BADARG,
+              "peer_gather: sizes and offsets must be multiples of 8 elements");
+  if (n == 0) return 0;
+  int64_t blocks = ((n >> 3) + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
+  peer_gather_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const bf16* const*>(peer_shards),
+                                                                   reinterpret_cast<bf16*>(unit_full), shard_elems, offset, n);
+  return check_launch("peer_gather");
 }
 
 int dla_fused_gather_dpo(float* const* peer_bufs, uint32_t* const* pads, int world, int rank, const float* pol_pos,

@@ -94,7 +94,11 @@ class _Linear(Function):
     @staticmethod
     def forward(ctx, x, w, bias):
         x2 = x.reshape(-1, x.shape[-1])
-        y = gemm(x2, w)
+        ag = getattr(w, "_ag", None)
+        if ag is not None and not ag.done:
+            y = ag.run(_c(x2))          # weight rows are all-gathered over NVLink inside this GEMM (path (b))
+        else:
+            y = gemm(x2, w)
         if bias is not None:
             N.call("dla_add_bias", N.ptr(y), None, N.ptr(bias), N.ptr(y), y.shape[0], y.shape[1], _s(y))
         ctx.save_for_backward(x2, w)

@@ -83,6 +83,14 @@ class Engine(ParamProvider):
                 self.fc = FusedComm.get(ctx)
             elif comm == "fused":
                 raise RuntimeError("hardware.comm=fused needs >= 2 CUDA ranks on NCCL with the native library built")
+        # streamed units (ZeRO-3 that does not fit resident): parameter all-gather fused into the consuming GEMMs
+        self.fused_stream = False
+        if comm in ("auto", "fused") and self.W > 1 and not self.resident:
+            from dla_b200.parallel.fused import FusedComm, fused_available
+
+            if fused_available(ctx):
+                self.fused_stream = True
+                self.fc = FusedComm.get(ctx)
         self.gred: Dict[str, torch.Tensor] = {}
         self.base: Dict[str, int] = {}
         self.full: Dict[str, Optional[torch.Tensor]] = {}
@@ -119,6 +127,19 @@ class Engine(ParamProvider):
                 off += self.P[u.name]
             self.param_arena = SymmetricArena(self.ctx, off, self.dtype)
             self.grad_arena = SymmetricArena(self.ctx, off, self.grad_dtype)
+        if self.fused_stream:
+            from dla_b200.parallel.fused import SymmetricArena
+
+            off, self.sbase = 0, {}
+            for u in self.units:
+                self.sbase[u.name] = off
+                off += self.S[u.name]
+            self.shard_arena = SymmetricArena(self.ctx, off, self.dtype)
+            self._ag_flags = torch.zeros(8192, dtype=torch.int32, device=self.device)
+            self._ag_epoch = 0
+            esz = _bytes(self.dtype)
+            self._unit_ptrs = {u.name: torch.tensor([ptr + self.sbase[u.name] * esz for ptr in self.shard_arena.ptrs],
+                                                    dtype=torch.int64, device=self.device) for u in self.units}
         for ui, u in enumerate(self.units):
             P, S = self.P[u.name], self.S[u.name]
             if self.fused:
@@ -130,7 +151,12 @@ class Engine(ParamProvider):
                 gen = torch.Generator(device=self.device).manual_seed(seed * 1000003 + ui)
                 init_unit_(full, u, self.cfg, gen)
             if self.W > 1:
-                self.shard[u.name] = full[self.r * S:(self.r + 1) * S].clone()
+                if self.fused_stream:
+                    sb = self.sbase[u.name]
+                    self.shard[u.name] = self.shard_arena.tensor[sb:sb + S]
+                    self.shard[u.name].copy_(full[self.r * S:(self.r + 1) * S])
+                else:
+                    self.shard[u.name] = full[self.r * S:(self.r + 1) * S].clone()
                 self.full[u.name] = full if self.resident else None
             else:
                 self.shard[u.name] = full            # the rank owns the whole unit
@@ -146,6 +172,9 @@ class Engine(ParamProvider):
             del full
         if self.trainable:
             self._init_optimizer_state()
+        if self.fused_stream:
+            torch.cuda.synchronize(self.device)
+            self.ctx.barrier()          # every rank's shards are in place before anyone pulls them
 
     def _init_optimizer_state(self) -> None:
         for u in self.units:
@@ -208,6 +237,8 @@ class Engine(ParamProvider):
     def acquire(self, unit: str, backward: bool = False) -> Weights:
         if unit in self._views:
             return self._views[unit]
+        if self.full.get(unit) is None and self.fused_stream:
+            return self._acquire_fused_stream(unit)
         if self.full.get(unit) is None:
             self._gather_async(unit)
             work, full = self._gather_work.pop(unit)
@@ -222,6 +253,40 @@ class Engine(ParamProvider):
             gb = self.gradbuf.get(unit)
             if gb is None:
                 gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
+                self.gradbuf[unit] = gb
+            g = unit_views(gb, spec)
+            for k, t in w.items():
+                t.requires_grad_(True)
+                t._grad_slot = g[k]
+        self._views[unit] = w
+        return w
+
+    def _acquire_fused_stream(self, unit: str) -> Weights:
+        """Streamed unit, fused path (b): big 2-D weights are NOT gathered here — each carries an ``_ag`` ticket
+        and the first GEMM that consumes it pulls its rows from the owners inside the kernel; only the small
+        parameters (norms, biases) and non-GEMM tables are gathered up front by a plain peer-load kernel."""
+        spec = self._by_name[unit]
+        P, S = self.P[unit], self.S[unit]
+        full = torch.empty(P, dtype=self.dtype, device=self.device)
+        offs = spec.offsets()
+        ptrs = self._unit_ptrs[unit]
+        w = unit_views(full, spec)
+        order = [p.name for p in spec.params]
+        for i, prm in enumerate(spec.params):
+            o, n = offs[prm.name]
+            end = offs[order[i + 1]][0] if i + 1 < len(order) else P
+            gemm_weight = (unit.startswith("layer.") and len(prm.shape) == 2 and prm.shape[1] % 8 == 0
+                           and prm.numel >= 256 * 64)
+            if gemm_weight:
+                w[prm.name]._ag = _AGTicket(self, unit, full, ptrs, S, o, prm.shape[0])
+            else:
+                self.fc.gather_range(ptrs, full, S, o, end - o)
+                self.stats["allgather_bytes"] += (end - o) * _bytes(self.dtype)
+        self.full[unit] = full
+        if self.trainable:
+            gb = self.gradbuf.get(unit)
+            if gb is None:
+                gb = torch.zeros(P, dtype=self.grad_dtype, device=self.device)
                 self.gradbuf[unit] = gb
             g = unit_views(gb, spec)
             for k, t in w.items():
@@ -371,6 +436,8 @@ class Engine(ParamProvider):
                 self.stats["allgather_bytes"] += self.P[u.name] * _bytes(self.dtype)
             for w in works:
                 w.wait()
+        if self.fused_stream:
+            self.fc.barrier(2)      # peers pull my shards inside their GEMMs: publish the updated ones first
         self.zero_grad()
 
     def _fused_optimizer_step(self, opt: AdamWConfig, lr: float, prescale: float, bc1: float, bc2: float) -> None:
@@ -475,6 +542,22 @@ class Engine(ParamProvider):
         own = tot(self.shard) if self.W > 1 else 0.0
         return {"params_full_gb": tot(self.full), "params_shard_gb": own, "grads_gb": tot(self.gradbuf) + tot(self.gshard),
                 "optimizer_gb": tot(self.master) + tot(self.m) + tot(self.v)}
+
+
+class _AGTicket:
+    """Deferred all-gather of one weight matrix: redeemed by the first GEMM that consumes it."""
+
+    def __init__(self, engine: "Engine", unit: str, full: torch.Tensor, ptrs: torch.Tensor, S: int, offset: int, n_out: int) -> None:
+        self.engine, self.unit, self.full, self.ptrs, self.S, self.offset, self.n_out = engine, unit, full, ptrs, S, offset, n_out
+        self.done = False
+
+    def run(self, x2: torch.Tensor) -> torch.Tensor:
+        eng = self.engine
+        eng._ag_epoch += 1
+        y = eng.fc.ag_gemm(x2, self.ptrs, self.full, self.S, self.offset, self.n_out, eng._ag_flags, eng._ag_epoch)
+        eng.stats["allgather_bytes"] += self.n_out * x2.shape[1] * _bytes(eng.dtype)
+        self.done = True
+        return y
 
 
 def _bytes(dt: torch.dtype) -> int:

@@ -106,6 +106,20 @@ class FusedComm:
     def push_shard(self, src: torch.Tensor, params: SymmetricArena, offset: int) -> None:
         N.call("dla_peer_push", N.ptr(src), params.ptrs_dev, self.W, self.r, offset, src.numel(), N.stream_ptr(self.ctx.device))
 
+    # ---------------------------------------------------------------- (b)
+    def gather_range(self, unit_ptrs: torch.Tensor, full: torch.Tensor, shard_elems: int, offset: int, n: int) -> None:
+        """full[offset : offset+n) <- the owners' shards (plain peer loads; small parameters of a streamed unit)."""
+        N.call("dla_peer_gather", N.ptr(unit_ptrs), N.ptr(full), shard_elems, offset, n, self.W, N.stream_ptr(self.ctx.device))
+
+    def ag_gemm(self, x2: torch.Tensor, unit_ptrs: torch.Tensor, full: torch.Tensor, shard_elems: int, b_offset: int,
+                n_out: int, flags: torch.Tensor, epoch: int, n_copy: int = 12) -> torch.Tensor:
+        """y = x2 @ W^T where W = full[b_offset : b_offset + n_out*K] is gathered from its owners INSIDE the GEMM."""
+        M, K = x2.shape
+        y = torch.empty(M, n_out, dtype=x2.dtype, device=x2.device)
+        N.call("dla_ag_gemm_bf16", N.ptr(x2), N.ptr(unit_ptrs), N.ptr(full), shard_elems, b_offset, N.ptr(y), M, n_out, K,
+               x2.stride(0), y.stride(0), self.W, self.r, N.ptr(flags), epoch, n_copy, 0, N.stream_ptr(x2.device))
+        return y
+
     # ---------------------------------------------------------------- (c)
     def dpo_loss(self, pol_pos, pol_neg, ref_pos, ref_neg, beta: float, label_smoothing: float):
         """Returns (global stats [loss, pref_rate, margin], dpos, dneg) — gradients are of the local-batch mean."""

@@ -214,12 +214,20 @@ int dla_peer_barrier(uint32_t* const* pads, int world, int rank, int channel, ui
                      int timeout_ms, void* stream);
 /* 1 if any peer-flag wait of this process timed out since load (synchronises the device). */
 int dla_peer_status(int* timed_out);
-/* (b) all-gather fused GEMM: C[M,N] = A[M,K] * Wfull[N,K]^T where Wfull's rows are sharded across
- * ranks (rank r owns rows [r*N/W, (r+1)*N/W)); B tiles are TMA-loaded straight from the owning
- * peer's memory (peer_maps built over peer pointers) into the tcgen05 pipeline. */
-int dla_ag_gemm_bf16(const void* A, const void* const* peer_B_host, void* C, int M, int N, int K,
-                     int64_t lda, int64_t ldb, int64_t ldc, int world, int c_fp32, int accumulate,
-                     void* stream);
+/* (b) all-gather fused GEMM: C[M,N] = A[M,K] * B[N,K]^T where B = unit_full + b_offset and the unit's
+ * elements are sharded contiguously across ranks (rank r owns [r*shard_elems, (r+1)*shard_elems); peer_shards:
+ * device array of `world` pointers to every rank's shard in peer-mapped memory).  ONE kernel: the first
+ * n_copy_ctas CTAs TMA-bulk-copy B's rows from their owners over NVLink into unit_full, tile by tile, publishing
+ * epoch-stamped flags; the other CTAs run the tcgen05 GEMM and consume each B tile as soon as its flag shows
+ * `epoch` (tiles owned by this rank first).  flags: uint32 [ceil(N/256)], reused across calls with a fresh epoch.
+ * R: NCCL all_gather_into_tensor + cuBLAS issued by FSDP/ZeRO-3 under R/src/training/train_dpo.py:32. */
+int dla_ag_gemm_bf16(const void* A, const void* const* peer_shards, void* unit_full, int64_t shard_elems,
+                     int64_t b_offset, void* C, int M, int N, int K, int64_t lda, int64_t ldc, int world,
+                     int rank, uint32_t* flags, uint32_t epoch, int n_copy_ctas, int c_fp32, void* stream);
+/* Plain peer gather of a flat range [offset, offset+n) of a sharded unit into unit_full (no GEMM): used for the
+ * small non-GEMM parameters of a streamed unit. */
+int dla_peer_gather(const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t offset, int64_t n,
+                    int world, void* stream);
 /* (c) cross-rank all-gather of per-sequence log-probs fused with the DPO loss: each rank writes its
  * [4, B] block into every peer's gather buffer, barriers, then reduces loss / preference rate /
  * margin over all W*B pairs and produces its local gradients. */

@@ -139,3 +139,84 @@ def test_fused_engine_matches_nccl_engine(tmp_path):
     assert gn == pytest.approx(gf, rel=2e-2)
     rel = float((pn - pf).norm() / pn.norm())
     assert rel < 2e-3, rel
+
+
+def _ag_worker(rank, world, port, out):
+    import torch.distributed as dist
+
+    ctx = _init(rank, world, port)
+    from dla_b200.parallel.fused import FusedComm, SymmetricArena
+
+    dev = ctx.device
+    fc = FusedComm.get(ctx)
+    # a "unit": [pad 512 elems | W (N x K) | tail 1024 elems], sharded contiguously over the ranks
+    M, N_, K = 640, 1536, 512
+    b_off = 512
+    P = b_off + N_ * K + 1024
+    P = -(-P // (8 * world)) * (8 * world)
+    S = P // world
+    g = torch.Generator(device=dev).manual_seed(7)                      # same "full unit" on every rank
+    unit = (torch.randn(P, device=dev, generator=g) * 0.05).to(torch.bfloat16)
+    shards = SymmetricArena(ctx, S, torch.bfloat16)
+    shards.tensor.copy_(unit[rank * S:(rank + 1) * S])
+    fc.barrier(0)
+    ptrs = torch.tensor(shards.ptrs, dtype=torch.int64, device=dev)
+    x = torch.randn(M, K, device=dev, generator=torch.Generator(device=dev).manual_seed(100 + rank)).to(torch.bfloat16)
+    flags = torch.zeros(64, dtype=torch.int32, device=dev)
+    for epoch in (1, 2):                                               # second call reuses the flags with a new epoch
+        full = torch.full((P,), float("nan"), device=dev, dtype=torch.bfloat16)
+        y = fc.ag_gemm(x, ptrs, full, S, b_off, N_, flags, epoch, n_copy=4)
+        torch.cuda.synchronize()
+        w = unit[b_off:b_off + N_ * K].view(N_, K)
+        assert torch.equal(full[b_off:b_off + N_ * K].view(N_, K), w), "gathered weight differs"
+        ref = x.float() @ w.float().t()
+        assert torch.allclose(y.float(), ref, atol=0.05, rtol=2e-2), (y.float() - ref).abs().max()
+    # plain peer gather of the tail
+    fc.gather_range(ptrs, full, S, b_off + N_ * K, 1024)
+    torch.cuda.synchronize()
+    assert torch.equal(full[b_off + N_ * K:b_off + N_ * K + 1024], unit[b_off + N_ * K:b_off + N_ * K + 1024])
+    fc.check()
+    ctx.barrier()
+
+
+def _e2e_stream_worker(rank, world, port, out):
+    ctx = _init(rank, world, port)
+    from dla_b200.algo import dpo_step
+    from dla_b200.config import HardwarePlan
+    from dla_b200.data.synthetic import synthetic_preference_batch
+    from dla_b200.models.factory import load_causal_lm
+    from dla_b200.optim import AdamWConfig
+
+    res = {}
+    for comm in ("nccl", "fused"):
+        plan = HardwarePlan(sharding="zero3", comm=comm, resident_params=False)
+        pol = load_causal_lm("tiny-llama", ctx, plan, seed=13, name=f"policy_{comm}")
+        ref = load_causal_lm("tiny-llama", ctx, plan, trainable=False, gradient_checkpointing=False, seed=13, name=f"ref_{comm}")
+        assert pol.engine.fused_stream == (comm == "fused") and not pol.engine.resident
+        losses = []
+        for step in range(3):
+            full = synthetic_preference_batch(2 * world, 128, pol.config.vocab_size, seed=70 + step, ragged=True)
+            batch = {s: {k: v[rank * 2:(rank + 1) * 2].cuda() for k, v in full[s].items()} for s in full}
+            loss, info = dpo_step(pol.model, ref.model, batch, beta=0.5)
+            loss.backward()
+            pol.engine.finish_backward()
+            pol.engine.optimizer_step(AdamWConfig(lr=1e-3, weight_decay=0.01, max_grad_norm=1.0), grad_divisor=float(world))
+            losses.append(float(ctx.all_reduce(loss.detach().clone(), "mean")))
+        flat = torch.cat([pol.engine.gathered_unit(u.name)[p.name].reshape(-1).float() for u in pol.engine.units for p in u.params])
+        res[comm] = (losses, flat.cpu())
+    if rank == 0:
+        torch.save(res, out)
+    ctx.barrier()
+
+
+def test_all_gather_fused_gemm_matches_gather_then_matmul(tmp_path):
+    mp.spawn(_ag_worker, args=(2, _free_port(), str(tmp_path / "x")), nprocs=2, join=True)
+
+
+def test_streamed_engine_with_fused_all_gather_matches_nccl(tmp_path):
+    out = tmp_path / "e2e_stream.pt"
+    mp.spawn(_e2e_stream_worker, args=(2, _free_port(), str(out)), nprocs=2, join=True)
+    res = torch.load(out)
+    (ln, pn), (lf, pf) = res["nccl"], res["fused"]
+    assert ln == pytest.approx(lf, abs=2e-3), (ln, lf)
+    assert float((pn - pf).norm() / pn.norm()) < 2e-3
