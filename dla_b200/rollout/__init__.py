@@ -110,7 +110,8 @@ class Generator:
         cache = KVCache(cfg, B, max_len, dev, dtype)
         Hq, Hk = cfg.num_heads, cfg.num_kv_heads
         gen = torch.Generator(device=dev)
-        gen.manual_seed(seed if seed is not None else int(torch.randint(0, 2**31 - 1, (1,)).item()))
+        seed = seed if seed is not None else int(torch.randint(0, 2**31 - 1, (1,)).item())
+        gen.manual_seed(seed)
 
         # ---- prefill: full causal attention over the (right-padded) prompts, filling the cache
         pos = torch.arange(Tp, device=dev, dtype=torch.int32).expand(B, Tp)
@@ -135,7 +136,7 @@ class Generator:
         rows = torch.arange(B, device=dev)
         steps = min(max_new_tokens, max_len - int(plen.min().item()))
         for step in range(steps):
-            nxt = sample(logits, temperature if do_sample else 0.0, top_p, gen)
+            nxt = sample(logits, temperature if do_sample else 0.0, top_p, gen, seed=seed, step=step)
             nxt = torch.where(finished, torch.full_like(nxt, pad), nxt)
             can = (~finished) & (lens < max_len)
             idx = lens.long().clamp(max=max_len - 1)
@@ -168,8 +169,20 @@ class Generator:
         return GenerationOutput(seqs, amask, plen.long(), rmask, lens.long())
 
 
-def sample(logits: torch.Tensor, temperature: float, top_p: float, generator: Optional[torch.Generator] = None) -> torch.Tensor:
-    """Next-token choice on the device: greedy when ``temperature <= 0`` else nucleus sampling."""
+def sample(logits: torch.Tensor, temperature: float, top_p: float, generator: Optional[torch.Generator] = None,
+           seed: int = 0, step: int = 0) -> torch.Tensor:
+    """Next-token choice on the device: greedy when ``temperature <= 0`` else nucleus sampling.  CUDA runs
+    the fused temperature + top-p + multinomial kernel (``csrc/sampler.cu``, counter-based RNG keyed by
+    ``seed``/``step``); CPU runs the sort-based PyTorch restatement."""
+    if logits.is_cuda:
+        lg = logits if logits.is_contiguous() else logits.contiguous()
+        if lg.dtype not in (torch.float32, torch.bfloat16):
+            lg = lg.float()
+        out = torch.empty(lg.shape[0], dtype=torch.int64, device=lg.device)
+        N.call("dla_sample_top_p", N.ptr(lg), int(lg.dtype == torch.float32), lg.shape[0], lg.shape[1], lg.stride(0),
+               float(temperature), float(min(max(top_p, 1e-6), 1.0)), int(seed) & 0xFFFFFFFFFFFFFFFF, int(step), None,
+               N.ptr(out), N.stream_ptr(lg.device))
+        return out
     if temperature <= 0:
         return logits.argmax(-1)
     return R.top_p_sample(logits, temperature, top_p, generator)

@@ -307,3 +307,33 @@ def test_attention_decode(native_lib):
            N.stream_ptr())
     ref = R.attention(q[:, None], kc, vc, causal=False, seqlens=lens)[:, 0]
     _close(o, ref, what="decode attention")
+
+
+def test_top_p_sampler_kernel(native_lib):
+    from dla_b200.rollout import sample
+
+    torch.manual_seed(14)
+    B, V = 6, 5003
+    logits = torch.randn(B, V, device=DEV) * 3
+    assert torch.equal(sample(logits, 0.0, 1.0), logits.argmax(-1))                 # greedy
+    assert torch.equal(sample(logits.to(BF16), 0.0, 1.0), logits.to(BF16).float().argmax(-1))
+    assert torch.equal(sample(logits, 0.7, 1e-6, seed=3), logits.argmax(-1))        # top_p -> 0 keeps only the mode
+    # every draw lies inside the nucleus the sort-based reference computes, and draws are reproducible
+    T, top_p = 0.8, 0.6
+    probs = torch.softmax(logits / T, -1)
+    sp, si = probs.sort(-1, descending=True)
+    keep = (sp.cumsum(-1) - sp) < top_p
+    nucleus = [set(si[b][keep[b]].tolist()) for b in range(B)]
+    draws = torch.stack([sample(logits, T, top_p, seed=11, step=s) for s in range(400)], 1)   # [B, 400]
+    assert torch.equal(draws[:, :5], torch.stack([sample(logits, T, top_p, seed=11, step=s) for s in range(5)], 1))
+    for b in range(B):
+        got = set(draws[b].tolist())
+        assert got <= nucleus[b], (b, sorted(got - nucleus[b])[:5])
+        if len(nucleus[b]) > 1:
+            assert len(got) > 1
+    # empirical frequency of the most likely token matches its renormalised probability
+    b = 0
+    top_tok = int(si[b, 0])
+    want = float(sp[b, 0] / sp[b][keep[b]].sum())
+    freq = float((draws[b] == top_tok).float().mean())
+    assert abs(freq - want) < 0.08, (freq, want)

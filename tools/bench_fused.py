@@ -1,0 +1,162 @@
+#!/usr/bin/env python
+"""Roofline numbers for the three fused compute+collective paths, N ranks on one box (torchrun).
+Device-timed (CUDA events), max over ranks, L2 irrelevant (buffers are hundreds of MB).
+
+  (a) per-unit gradient reduce-scatter + scale + norm partial (fused peer reads) vs NCCL reduce_scatter_tensor
+      + cast + sumsq, and the full optimizer step (fused vs NCCL engine) on Llama-3-8B-sized units
+  (b) all-gather fused GEMM vs NCCL all_gather_into_tensor + tcgen05 GEMM, on the QKV and gate-up shapes
+  (c) fused gather + DPO loss vs all_gather x4 + loss kernel
+
+Writes gpurun_out/fused_paths_N<world>.json (rank 0)."""
+import json
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT))
+
+from dla_b200.ops import functional as F  # noqa: E402
+from dla_b200.ops import native as N  # noqa: E402
+from dla_b200.parallel.fused import FusedComm, SymmetricArena  # noqa: E402
+from dla_b200.parallel.pg import init_distributed  # noqa: E402
+
+NVLINK_GBS = 770.0          # measured peer-copy bandwidth per direction (B200_PROFILING.md)
+ctx = init_distributed()
+W, r, dev = ctx.world_size, ctx.rank, ctx.device
+fc = FusedComm.get(ctx)
+
+
+def timed(fn, iters=10, warm=3):
+    for _ in range(warm):
+        fn()
+    ctx.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return ctx.max_over_ranks(e0.elapsed_time(e1) / iters)
+
+
+out = {"world": W, "nvlink_gbs_per_dir": NVLINK_GBS}
+
+# ---------------------------------------------------------------- (a)
+P = 218_112_000                      # one Llama-3-8B decoder layer
+P = -(-P // (8 * W)) * (8 * W)
+S = P // W
+grads = SymmetricArena(ctx, P, torch.bfloat16)
+grads.tensor.normal_()
+params = SymmetricArena(ctx, P, torch.bfloat16)
+gred = torch.empty(S, device=dev)
+sumsq = torch.zeros(1, device=dev)
+master, m_, v_ = (torch.zeros(S, device=dev) for _ in range(3))
+
+
+def fused_a():
+    fc.barrier(0)
+    fc.reduce_shard(grads, r * S, S, 1.0 / W, gred, sumsq)
+
+
+nccl_out = torch.empty(S, device=dev, dtype=torch.bfloat16)
+scratch = torch.empty(N.sumsq_blocks(), device=dev)
+
+
+def nccl_a():
+    dist.reduce_scatter_tensor(nccl_out, grads.tensor, group=ctx.group)
+    N.call("dla_sumsq", N.ptr(nccl_out), S, 0, N.ptr(scratch), N.ptr(sumsq), 1, N.stream_ptr())
+
+
+def fused_a_full():
+    fc.barrier(0)
+    fc.reduce_adamw_push(grads, params, r * S, S, 1.0 / W, master, m_, v_, 1e-6, (0.9, 0.999), 1e-8, 0.01, 0.1, 0.001, None)
+    fc.barrier(0)
+
+
+shard_bf16 = torch.empty(S, device=dev, dtype=torch.bfloat16)
+
+
+def nccl_a_full():
+    dist.reduce_scatter_tensor(nccl_out, grads.tensor, group=ctx.group)
+    N.call("dla_adamw", N.ptr(master), N.ptr(m_), N.ptr(v_), N.ptr(nccl_out), N.ptr(shard_bf16), S, 1e-6, 0.9, 0.999, 1e-8, 0.01,
+           0.1, 0.001, None, 1.0 / W, 0, N.stream_ptr())
+    dist.all_gather_into_tensor(params.tensor, shard_bf16, group=ctx.group)
+
+
+link_bytes = (W - 1) * S * 2                      # bytes each rank must pull over NVLink
+t_fa, t_na = timed(fused_a), timed(nccl_a)
+t_faf, t_naf = timed(fused_a_full), timed(nccl_a_full)
+roof_a = link_bytes / (NVLINK_GBS * 1e9) * 1e3
+roof_af = max(2 * link_bytes / 2, link_bytes) / (NVLINK_GBS * 1e9) * 1e3      # pull grads (in) and push params (out) use opposite directions
+out["a_reduce_scatter_norm"] = {"unit_elems": P, "fused_ms": t_fa, "nccl_ms": t_na, "roofline_ms": roof_a,
+                                "fused_frac_of_roofline": roof_a / t_fa, "nccl_frac_of_roofline": roof_a / t_na}
+out["a_reduce_adamw_allgather"] = {"fused_ms": t_faf, "nccl_ms": t_naf, "roofline_ms": roof_af,
+                                   "fused_frac_of_roofline": roof_af / t_faf, "nccl_frac_of_roofline": roof_af / t_naf}
+
+# ---------------------------------------------------------------- (b)
+bf16_tflops = 1632.6
+try:
+    bf16_tflops = json.load(open(ROOT / "MEASURED_PEAKS.json"))["bf16_tflops"]
+except Exception:
+    pass
+res_b = {}
+for tag, Nn, K in (("qkv", 6144, 4096), ("gate_up", 28672, 4096)):
+    M = 8192
+    unit = -(-Nn * K // (8 * W)) * (8 * W)
+    Sb = unit // W
+    shards = SymmetricArena(ctx, Sb, torch.bfloat16)
+    shards.tensor.normal_(std=0.02)
+    ptrs = torch.tensor(shards.ptrs, dtype=torch.int64, device=dev)
+    full = torch.empty(unit, device=dev, dtype=torch.bfloat16)
+    x = torch.randn(M, K, device=dev).to(torch.bfloat16)
+    flags = torch.zeros(256, dtype=torch.int32, device=dev)
+    ep = [0]
+
+    def fused_b():
+        ep[0] += 1
+        fc.ag_gemm(x, ptrs, full, Sb, 0, Nn, flags, ep[0], n_copy=12)
+
+    y = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
+
+    def nccl_b():
+        dist.all_gather_into_tensor(full, shards.tensor, group=ctx.group)
+        F.gemm(x, full[:Nn * K].view(Nn, K), out=y)
+
+    def gemm_only():
+        F.gemm(x, full[:Nn * K].view(Nn, K), out=y)
+
+    fc.barrier(0)
+    t_f, t_n, t_g = timed(fused_b), timed(nccl_b), timed(gemm_only)
+    flops = 2.0 * M * Nn * K
+    roof = max(flops / (bf16_tflops * 1e12), (W - 1) * Sb * 2 / (NVLINK_GBS * 1e9)) * 1e3
+    res_b[tag] = {"M": M, "N": Nn, "K": K, "fused_ms": t_f, "nccl_ag_plus_gemm_ms": t_n, "gemm_only_ms": t_g, "roofline_ms": roof,
+                  "fused_frac_of_roofline": roof / t_f, "nccl_frac_of_roofline": roof / t_n}
+out["b_all_gather_gemm"] = res_b
+
+# ---------------------------------------------------------------- (c)
+B = 4
+pp, pn, rp, rn = (torch.randn(B, device=dev) for _ in range(4))
+
+
+def fused_c():
+    fc.dpo_loss(pp, pn, rp, rn, 0.1, 0.0)
+
+
+def nccl_c():
+    g = [ctx.gather(t) for t in (pp, pn, rp, rn)]
+    F.dpo_loss(g[0], g[1], g[2], g[3], 0.1)
+
+
+out["c_gather_dpo_loss"] = {"pairs_per_rank": B, "fused_us": timed(fused_c, 50) * 1e3, "nccl_us": timed(nccl_c, 50) * 1e3,
+                            "note": "latency-bound: O(B) floats; roofline = one NVLink round trip (~2-4 us)"}
+fc.check()
+if ctx.is_main:
+    Path(ROOT / "gpurun_out").mkdir(exist_ok=True)
+    json.dump(out, open(ROOT / "gpurun_out" / f"fused_paths_N{W}.json", "w"), indent=1)
+    print(json.dumps(out, indent=1))
+ctx.barrier()
