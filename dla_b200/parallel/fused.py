@@ -112,7 +112,7 @@ class FusedComm:
         N.call("dla_peer_gather", N.ptr(unit_ptrs), N.ptr(full), shard_elems, offset, n, self.W, N.stream_ptr(self.ctx.device))
 
     def ag_gemm(self, x2: torch.Tensor, unit_ptrs: torch.Tensor, full: torch.Tensor, shard_elems: int, b_offset: int,
-                n_out: int, flags: torch.Tensor, epoch: int, n_copy: int = 12) -> torch.Tensor:
+                n_out: int, flags: torch.Tensor, epoch: int, n_copy: int = 8) -> torch.Tensor:
         """y = x2 @ W^T where W = full[b_offset : b_offset + n_out*K] is gathered from its owners INSIDE the GEMM."""
         M, K = x2.shape
         y = torch.empty(M, n_out, dtype=x2.dtype, device=x2.device)

@@ -117,9 +117,11 @@ for tag, Nn, K in (("qkv", 6144, 4096), ("gate_up", 28672, 4096)):
     flags = torch.zeros(256, dtype=torch.int32, device=dev)
     ep = [0]
 
+    ncopy = [12]
+
     def fused_b():
         ep[0] += 1
-        fc.ag_gemm(x, ptrs, full, Sb, 0, Nn, flags, ep[0], n_copy=12)
+        fc.ag_gemm(x, ptrs, full, Sb, 0, Nn, flags, ep[0], n_copy=ncopy[0])
 
     y = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
 
@@ -131,10 +133,16 @@ for tag, Nn, K in (("qkv", 6144, 4096), ("gate_up", 28672, 4096)):
         F.gemm(x, full[:Nn * K].view(Nn, K), out=y)
 
     fc.barrier(0)
-    t_f, t_n, t_g = timed(fused_b), timed(nccl_b), timed(gemm_only)
+    sweep = {}
+    for nc in (2, 4, 8, 12, 16):
+        ncopy[0] = nc
+        sweep[nc] = timed(fused_b)
+    best = min(sweep, key=sweep.get)
+    ncopy[0] = best
+    t_f, t_n, t_g = sweep[best], timed(nccl_b), timed(gemm_only)
     flops = 2.0 * M * Nn * K
     roof = max(flops / (bf16_tflops * 1e12), (W - 1) * Sb * 2 / (NVLINK_GBS * 1e9)) * 1e3
-    res_b[tag] = {"M": M, "N": Nn, "K": K, "fused_ms": t_f, "nccl_ag_plus_gemm_ms": t_n, "gemm_only_ms": t_g, "roofline_ms": roof,
+    res_b[tag] = {"M": M, "N": Nn, "K": K, "copy_cta_sweep_ms": sweep, "copy_ctas": best, "fused_ms": t_f, "nccl_ag_plus_gemm_ms": t_n, "gemm_only_ms": t_g, "roofline_ms": roof,
                   "fused_frac_of_roofline": roof / t_f, "nccl_frac_of_roofline": roof / t_n}
 out["b_all_gather_gemm"] = res_b
 
