@@ -168,6 +168,41 @@ peer_push_kernel(const bf16* __restrict__ src, bf16* const* peers, int world, in
   }
 }
 
+// all-reduce by peer loads + peer stores (DDP gradients): this rank owns 1/world of [offset, offset+n):
+// it sums that slice over all ranks in fp32, scales, and writes the bf16 result into EVERY rank's buffer.
+__global__ void __launch_bounds__(256)
+peer_allreduce_kernel(bf16* const* peers, int world, int rank, int64_t offset, int64_t n, float scale) {
+  const int64_t slice = n / world;
+  const int64_t base = offset + slice * rank;
+  const int64_t nvec = slice >> 3;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t e = base + i * 8;
+    uint4 raw[kMaxWorld];
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < world) raw[r] = ld_peer16(peers[(r + rank) % world] + e);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r) {
+      if (r < world) {
+        float f[8];
+        unpack8(*reinterpret_cast<const bf16x8*>(&raw[r]), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += f[j];
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= scale;
+    const bf16x8 packed = pack8(acc);
+    const uint4 u = *reinterpret_cast<const uint4*>(&packed);
+#pragma unroll
+    for (int r = 0; r < kMaxWorld; ++r)
+      if (r < world) st_peer16(peers[(r + rank) % world] + e, u);
+  }
+}
+
 // gather a flat range of a sharded unit: element e comes from rank e / S at offset e % S
 __global__ void __launch_bounds__(256)
 peer_gather_kernel(const bf16* const* peers, bf16* __restrict__ full, int64_t S, int64_t offset, int64_t n) {
@@ -310,6 +345,18 @@ int dla_peer_push(const void* src, void* const* peers, int world, int rank, int6
   if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
   peer_push_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)src, reinterpret_cast<bf16* const*>(peers), world, rank, dst_offset, n);
   return check_launch("peer_push");
+}
+
+int dla_peer_allreduce(void* const* peers, int world, int rank, int64_t offset, int64_t n, float scale, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, DLA_E_BADARG, "peer_allreduce: bad world/rank");
+  DLA_REQUIRE(n % (8 * world) == 0 && offset % 8 == 0, DLA_E_BADARG, "peer_allreduce: n must be a multiple of 8*world elements");
+  if (n == 0) return 0;
+  int64_t blocks = ((n / world >> 3) + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 8) blocks = (int64_t)kNumSMs * 8;
+  if (blocks < 1) blocks = 1;
+  peer_allreduce_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<bf16* const*>(peers), world, rank, offset, n, scale);
+  return check_launch("peer_allreduce");
 }
 
 int dla_peer_gather(const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t offset, int64_t n, int world,

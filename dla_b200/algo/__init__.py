@@ -71,7 +71,7 @@ def dpo_step(policy: CausalLM, ref: CausalLM, batch: Dict[str, Dict[str, torch.T
             ref_pos = sequence_logprobs(ref, ch["input_ids"], ch["attention_mask"], reduction)
             ref_neg = sequence_logprobs(ref, rj["input_ids"], rj["attention_mask"], reduction)
     eng = policy.p
-    if getattr(eng, "fused", False) and pol_pos.is_cuda and torch.is_grad_enabled():
+    if (getattr(eng, "fused", False) or getattr(eng, "fused_ddp", False)) and pol_pos.is_cuda and torch.is_grad_enabled():
         # fused path (c): the cross-rank gather of the four log-prob vectors happens inside the loss kernel
         # over NVLink peer memory; loss / preference rate / margin are GLOBAL-batch statistics
         from dla_b200.parallel.fused import fused_dpo_loss

@@ -54,6 +54,7 @@ _SIGNATURES = {
     "dla_peer_barrier": [P, I, I, I, c_uint32, I, P],
     "dla_peer_push": [P, P, I, I, I64, I64, P],
     "dla_peer_gather": [P, P, I64, I64, I64, I, P],
+    "dla_peer_allreduce": [P, I, I, I64, I64, F, P],
     "dla_ag_gemm_bf16": [P, P, P, I64, I64, P, I, I, I, I64, I64, I, I, P, c_uint32, I, I, P],
     "dla_fused_gather_dpo": [P, P, I, I, P, P, P, P, I, F, F, c_uint32, P, P, P, P],
 }

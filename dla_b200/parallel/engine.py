@@ -83,6 +83,15 @@ class Engine(ParamProvider):
                 self.fc = FusedComm.get(ctx)
             elif comm == "fused":
                 raise RuntimeError("hardware.comm=fused needs >= 2 CUDA ranks on NCCL with the native library built")
+        # replicated (DDP) mode over peer memory: gradient buckets live in a symmetric arena and are all-reduced
+        # by one reduce-and-push kernel instead of bucketed NCCL all_reduce calls
+        self.fused_ddp = False
+        if comm in ("auto", "fused") and trainable and self.sharding == "ddp" and ctx.world_size > 1:
+            from dla_b200.parallel.fused import FusedComm, fused_available
+
+            if fused_available(ctx):
+                self.fused_ddp = True
+                self.fc = FusedComm.get(ctx)
         # streamed units (ZeRO-3 that does not fit resident): parameter all-gather fused into the consuming GEMMs
         self.fused_stream = False
         if comm in ("auto", "fused") and self.W > 1 and not self.resident:
@@ -127,6 +136,15 @@ class Engine(ParamProvider):
                 off += self.P[u.name]
             self.param_arena = SymmetricArena(self.ctx, off, self.dtype)
             self.grad_arena = SymmetricArena(self.ctx, off, self.grad_dtype)
+        if self.fused_ddp:
+            from dla_b200.parallel.fused import SymmetricArena
+
+            off = 0
+            for u in self.units:
+                self.base[u.name] = off
+                off += self.P[u.name]
+            self._ddp_total = -(-off // (8 * self.ctx.world_size)) * (8 * self.ctx.world_size)
+            self.grad_arena = SymmetricArena(self.ctx, self._ddp_total, self.grad_dtype)
         if self.fused_stream:
             from dla_b200.parallel.fused import SymmetricArena
 
@@ -162,7 +180,9 @@ class Engine(ParamProvider):
                 self.shard[u.name] = full            # the rank owns the whole unit
                 self.full[u.name] = full
             if self.trainable:
-                if self.fused:
+                if self.fused_ddp:
+                    self.gradbuf[u.name] = self.grad_arena.tensor[self.base[u.name]:self.base[u.name] + P]
+                elif self.fused:
                     self.gradbuf[u.name] = self.grad_arena.tensor[self.base[u.name]:self.base[u.name] + P]
                     self.gred[u.name] = torch.zeros(S, dtype=torch.float32, device=self.device)
                 else:
@@ -321,8 +341,8 @@ class Engine(ParamProvider):
             self._launch_reduce(unit)               # streamed units reduce-scatter every micro-step
 
     def _launch_reduce(self, unit: str) -> None:
-        if self.fused:
-            return          # peers pull this bucket themselves inside the fused kernel (optimizer_step)
+        if self.fused or self.fused_ddp:
+            return          # peers pull this bucket themselves inside the fused kernels
         gb = self.gradbuf[unit]
         nbytes = gb.numel() * gb.element_size()
         self.stats["reduce_bytes"] += nbytes
@@ -362,6 +382,9 @@ class Engine(ParamProvider):
         self._drain(0)
         if self.fused and self.sync_grads:
             self.fc.barrier(0)      # every rank's gradient buckets are complete before anyone reads them
+        if self.fused_ddp and self.sync_grads:
+            self.fc.all_reduce_(self.grad_arena, 0, self._ddp_total)
+            self.stats["reduce_bytes"] += self._ddp_total * _bytes(self.grad_dtype)
 
     # ------------------------------------------------------------------ optimizer
     def _local_grad(self, unit: str) -> torch.Tensor:

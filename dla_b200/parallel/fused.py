@@ -106,6 +106,13 @@ class FusedComm:
     def push_shard(self, src: torch.Tensor, params: SymmetricArena, offset: int) -> None:
         N.call("dla_peer_push", N.ptr(src), params.ptrs_dev, self.W, self.r, offset, src.numel(), N.stream_ptr(self.ctx.device))
 
+    def all_reduce_(self, arena: SymmetricArena, offset: int, n: int, scale: float = 1.0) -> None:
+        """In-place sum over ranks of ``arena[offset : offset+n)`` on every rank (DDP gradients): barrier,
+        reduce-my-slice-and-push kernel, barrier."""
+        self.barrier(0)
+        N.call("dla_peer_allreduce", arena.ptrs_dev, self.W, self.r, offset, n, scale, N.stream_ptr(self.ctx.device))
+        self.barrier(0)
+
     # ---------------------------------------------------------------- (b)
     def gather_range(self, unit_ptrs: torch.Tensor, full: torch.Tensor, shard_elems: int, offset: int, n: int) -> None:
         """full[offset : offset+n) <- the owners' shards (plain peer loads; small parameters of a streamed unit)."""

@@ -208,6 +208,11 @@ int dla_fused_rs_adamw(const void* const* peer_grads, void* const* peer_params, 
  * (peers: device array of `world` base pointers).  n and dst_offset multiples of 8. */
 int dla_peer_push(const void* src, void* const* peers, int world, int rank, int64_t dst_offset,
                   int64_t n, void* stream);
+/* All-reduce (sum * scale) of the bf16 range [offset, offset+n) of a symmetric buffer, in place on every rank:
+ * each rank reduces 1/world of the range from all peers over NVLink and stores the result into all of them.
+ * Bracket with dla_peer_barrier on both sides.  n % (8*world) == 0.  R: DDP's bucketed NCCL all_reduce under
+ * accelerator.backward (R/src/training/train_dpo.py:118; SURVEY C1, worklist #14). */
+int dla_peer_allreduce(void* const* peers, int world, int rank, int64_t offset, int64_t n, float scale, void* stream);
 /* Signal-pad barrier across ranks (system-scope release/acquire flags in peer memory).
  * pads: device array of W pointers to each rank's uint32 pad [W * channels]. */
 int dla_peer_barrier(uint32_t* const* pads, int world, int rank, int channel, uint32_t epoch,

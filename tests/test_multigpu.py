@@ -220,3 +220,42 @@ def test_streamed_engine_with_fused_all_gather_matches_nccl(tmp_path):
     (ln, pn), (lf, pf) = res["nccl"], res["fused"]
     assert ln == pytest.approx(lf, abs=2e-3), (ln, lf)
     assert float((pn - pf).norm() / pn.norm()) < 2e-3
+
+
+def _e2e_ddp_worker(rank, world, port, out):
+    ctx = _init(rank, world, port)
+    from dla_b200.algo import dpo_step
+    from dla_b200.config import HardwarePlan
+    from dla_b200.data.synthetic import synthetic_preference_batch
+    from dla_b200.models.factory import load_causal_lm
+    from dla_b200.optim import AdamWConfig
+
+    res = {}
+    for comm in ("nccl", "fused"):
+        plan = HardwarePlan(sharding="ddp", comm=comm)
+        pol = load_causal_lm("tiny-llama", ctx, plan, seed=17, name=f"policy_{comm}")
+        ref = load_causal_lm("tiny-llama", ctx, plan, trainable=False, gradient_checkpointing=False, seed=17, name=f"ref_{comm}")
+        assert pol.engine.fused_ddp == (comm == "fused") and pol.engine.W == 1
+        for step in range(3):
+            full = synthetic_preference_batch(2 * world, 128, pol.config.vocab_size, seed=90 + step, ragged=True)
+            batch = {s: {k: v[rank * 2:(rank + 1) * 2].cuda() for k, v in full[s].items()} for s in full}
+            loss, info = dpo_step(pol.model, ref.model, batch, beta=0.5)
+            loss.backward()
+            pol.engine.finish_backward()
+            pol.engine.optimizer_step(AdamWConfig(lr=1e-3, weight_decay=0.01, max_grad_norm=1.0), grad_divisor=float(world))
+        flat = torch.cat([pol.engine.gathered_unit(u.name)[p.name].reshape(-1).float() for u in pol.engine.units for p in u.params])
+        # replicas must stay identical across ranks
+        mx = flat.clone()
+        ctx.all_reduce(mx, "max")
+        assert torch.equal(mx, flat), "DDP replicas diverged"
+        res[comm] = flat.cpu()
+    if rank == 0:
+        torch.save(res, out)
+    ctx.barrier()
+
+
+def test_replicated_engine_with_peer_allreduce_matches_nccl(tmp_path):
+    out = tmp_path / "e2e_ddp.pt"
+    mp.spawn(_e2e_ddp_worker, args=(2, _free_port(), str(out)), nprocs=2, join=True)
+    res = torch.load(out)
+    assert float((res["nccl"] - res["fused"]).norm() / res["nccl"].norm()) < 2e-3

@@ -1,0 +1,9 @@
+#!/usr/bin/env bash
+# Race / memory checking of the native kernels on one GPU.  One tool per invocation — running
+# several compute-sanitizer tools in one call has left B200 boxes unusable (B200_PROFILING.md).
+#   tools/sanitize.sh memcheck|racecheck|synccheck|initcheck [pytest -k expression]
+set -euo pipefail
+cd "$(dirname "$0")/.."
+TOOL=${1:-memcheck}
+EXPR=${2:-"rmsnorm or swiglu or rope or losses or adamw"}
+exec compute-sanitizer --tool "$TOOL" --error-exitcode 1 python -m pytest tests/test_gpu_kernels.py -x -q -k "$EXPR" -p no:cacheprovider
