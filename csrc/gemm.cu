@@ -563,6 +563,7 @@ logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, co
 }
 
 static int g_variant = 0;
+static int g_auto_2cta = 1;      // measured on B200: faster than the 1-CTA kernel for K <= 16K (profiles/kernels_r1.jsonl)
 
 template <bool kAMN, bool kBMN, int kEpi>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
@@ -593,6 +594,11 @@ static int build_maps(CUtensorMap* tmA, CUtensorMap* tmB, const void* A, const v
 }  // namespace gemm
 }  // namespace dla
 
+namespace dla {
+int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                   int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream);
+}
+
 using namespace dla;
 using namespace dla::gemm;
 
@@ -620,6 +626,10 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   const int64_t esz = c_fp32 ? 4 : 2;
   const bool tma_ok = (((uintptr_t)C & 15) == 0) && ((ldc * esz) % 16 == 0) && g_variant != 1;
   p.store_mode = tma_ok ? 0 : 1;
+  // 2-CTA (cta_group::2) kernel: 256x256 cluster tiles; worth it once there is about a wave of them
+  const int64_t tiles2 = (int64_t)((M + 255) / 256) * ((N + 255) / 256);
+  if (tma_ok && (g_variant == 2 || (g_variant == 0 && g_auto_2cta && tiles2 >= kNumSMs / 2 && M >= 256 && K <= 16384)))
+    return gemm2_dispatch(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, c_fp32, accumulate, (cudaStream_t)stream);
   CUtensorMap tmC{};
   if (tma_ok) {
     rc = make_tmap_2d(&tmC, C, c_fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (int)esz, (uint64_t)N,

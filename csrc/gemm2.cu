@@ -1,0 +1,291 @@
+// 2-CTA (cta_group::2) variant of the bf16 GEMM: a cluster of two CTAs on one TPC computes a 256x256 tile
+// with ONE tcgen05.mma.cta_group::2 stream issued by the leader CTA.  Each CTA stages only its 128 rows of A
+// and its 128-row half of B per k-block (32 KiB instead of 48 KiB), so the tensor core's shared-memory
+// operand traffic per SM drops by a third and the ring deepens to 6 stages; accumulators stay split across
+// the two CTAs' TMEM (128 lanes x 256 columns each, double buffered).
+//
+//   warp 0  TMA producer (both CTAs; transaction bytes are signalled on the LEADER's full barrier)
+//   warp 1  MMA issuer (leader only); tcgen05.commit multicasts "slot free" / "accumulator ready" to both CTAs
+//   warps 2-5 epilogue (each CTA drains its own TMEM half through staged smem + TMA store / reduce-add)
+//
+// Same operand-layout support as gemm.cu (K-major / MN-major A and B).  Selected by dla_gemm_bf16 when the
+// problem has at least one full wave of 256x256 tiles (see gemm.cu) or forced with dla_gemm_set_variant(2).
+#include <math.h>
+
+#include "tc_common.cuh"
+
+namespace dla {
+namespace gemm2 {
+
+constexpr int BM = 128;            // A rows per CTA (cluster tile M = 256)
+constexpr int BNH = 128;           // B rows per CTA (cluster tile N = 256)
+constexpr int BN = 256;
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int kStages = 6;
+constexpr int A_BYTES = BM * BK * 2;     // 16 KiB
+constexpr int B_BYTES = BNH * BK * 2;    // 16 KiB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int kThreads = 192;
+constexpr int kEpiWarps = 4;
+constexpr int EPI_BYTES = kEpiWarps * 2 * 4096;
+constexpr int SMEM_BYTES = kStages * STAGE_BYTES + EPI_BYTES + 1024 + 256;
+constexpr int GROUP_M = 8;
+
+struct Params {
+  int M, N, K;
+  int c_fp32, accumulate;
+  int num_m_tiles, num_n_tiles;      // in 256 x 256 cluster tiles
+};
+
+__device__ __forceinline__ uint32_t pack2(uint32_t a, uint32_t b) {
+  bf162 v = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b));
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int& m_blk, int& n_blk) {
+  const int per_group = GROUP_M * num_n;
+  const int g = t / per_group;
+  const int first_m = g * GROUP_M;
+  const int gsz = min(num_m - first_m, GROUP_M);
+  const int r = t - g * per_group;
+  m_blk = first_m + r % gsz;
+  n_blk = r / gsz;
+}
+
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_smem_addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_smem_addr), "r"(cta));
+  return r;
+}
+
+// 2-CTA TMA load: data into THIS CTA's smem, completion bytes onto the barrier at cluster address `bar_cluster`
+__device__ __forceinline__ void tma_load_2d_to(void* smem_dst, const CUtensorMap* m, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          tc::smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+template <bool kAMN, bool kBMN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+             const __grid_constant__ CUtensorMap tmC, const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* epi_smem = smem + kStages * STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi_smem + EPI_BYTES);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = tc::cluster_ctarank();
+  const bool leader = cta == 0;
+  const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+  const int num_kb = (p.K + BK - 1) / BK;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tc::prefetch_tmap(&tmA);
+    tc::prefetch_tmap(&tmB);
+    tc::prefetch_tmap(&tmC);
+    for (int s = 0; s < kStages; ++s) {
+      tc::mbar_init(&full_bar[s], 1);        // leader's producer arrives once (+ tx bytes of both CTAs)
+      tc::mbar_init(&empty_bar[s], 1);       // one multicast commit per use
+    }
+    for (int a = 0; a < 2; ++a) {
+      tc::mbar_init(&tfull_bar[a], 1);
+      tc::mbar_init(&tempty_bar[a], 2 * kEpiWarps);   // epilogue warps of BOTH CTAs (used in the leader only)
+    }
+    tc::fence_barrier_init();
+  }
+  tc::cluster_sync();                          // peer barriers are initialised before anyone signals them
+  if (warp == 1) tc::tmem_alloc<2>(tmem_holder, 512);
+  tc::tc_fence_before();
+  tc::cluster_sync();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = cluster_id; t < num_tiles; t += n_clusters) {
+        int m_blk, n_blk;
+        tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+        const int m0 = m_blk * 256 + (int)cta * BM, n0 = n_blk * BN + (int)cta * BNH;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * STAGE_BYTES;
+          uint8_t* sb = sa + A_BYTES;
+          const uint32_t bar = mapa_u32(tc::smem_u32(&full_bar[stage]), 0);     // the leader's barrier
+          if (leader) tc::mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+          const int k0 = kb * BK;
+          if constexpr (!kAMN) {
+            tma_load_2d_to(sa, &tmA, bar, k0, m0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BM / 64; ++c) tma_load_2d_to(sa + c * (64 * BK * 2), &tmA, bar, m0 + c * 64, k0);
+          }
+          if constexpr (!kBMN) {
+            tma_load_2d_to(sb, &tmB, bar, k0, n0);
+          } else {
+#pragma unroll
+            for (int c = 0; c < BNH / 64; ++c) tma_load_2d_to(sb + c * (64 * BK * 2), &tmB, bar, n0 + c * 64, k0);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(256, BN, kAMN ? 1 : 0, kBMN ? 1 : 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int it = 0;
+      for (int t = cluster_id; t < num_tiles; t += n_clusters, ++it) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1;
+        tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          tc::mbar_wait(&full_bar[stage], phase);
+          tc::tc_fence_after();
+          const uint32_t sa = tc::smem_u32(smem + stage * STAGE_BYTES);
+          const uint32_t sb = sa + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t da = kAMN ? tc::make_smem_desc(sa + k * 2048, 64 * BK * 2, 1024) : tc::make_smem_desc(sa + k * 32, 16, 1024);
+            const uint64_t db = kBMN ? tc::make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024) : tc::make_smem_desc(sb + k * 32, 16, 1024);
+            tc::umma_bf16<2>(tmem_d, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+          }
+          tc::umma_commit_2sm(&empty_bar[stage], 0b11);                      // both CTAs' smem slots are reusable
+          if (kb == num_kb - 1) tc::umma_commit_2sm(&tfull_bar[acc], 0b11);  // both CTAs' accumulator halves are ready
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5 of both CTAs) =====================
+    const int quarter = warp & 3;
+    const uint32_t tempty_leader0 = mapa_u32(tc::smem_u32(&tempty_bar[0]), 0);
+    const uint32_t tempty_leader1 = mapa_u32(tc::smem_u32(&tempty_bar[1]), 0);
+    int it = 0;
+    for (int t = cluster_id; t < num_tiles; t += n_clusters, ++it) {
+      int m_blk, n_blk;
+      tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      tc::mbar_wait(&tfull_bar[acc], acc_phase);
+      tc::tc_fence_after();
+      const int col_base = n_blk * BN;
+      const int r0 = m_blk * 256 + (int)cta * BM + quarter * 32;
+      const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
+      const int gc = p.c_fp32 ? 32 : 64;
+      const int n_groups = BN / gc;
+      uint8_t* stage_base = epi_smem + (warp - 2) * 2 * 4096;
+#pragma unroll 1
+      for (int gi = 0; gi < n_groups; ++gi) {
+        uint8_t* buf = stage_base + (gi & 1) * 4096;
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        __syncwarp();
+        uint8_t* myrow = buf + lane * 128;
+        if (p.c_fp32) {
+          uint32_t r[32];
+          tc::tmem_ld_32x32(taddr + gi * 32, r);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 8; ++c)
+            *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = make_uint4(r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
+        } else {
+          uint32_t r[64];
+          tc::tmem_ld_32x32(taddr + gi * 64, r);
+          tc::tmem_ld_32x32(taddr + gi * 64 + 32, r + 32);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 v;
+            v.x = pack2(r[8 * c], r[8 * c + 1]);
+            v.y = pack2(r[8 * c + 2], r[8 * c + 3]);
+            v.z = pack2(r[8 * c + 4], r[8 * c + 5]);
+            v.w = pack2(r[8 * c + 6], r[8 * c + 7]);
+            *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = v;
+          }
+        }
+        tc::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          const int c0 = col_base + gi * gc;
+          if (c0 < p.N && r0 < p.M) {
+            if (p.accumulate) tc::tma_reduce_add_2d(&tmC, buf, c0, r0);
+            else tc::tma_store_2d(&tmC, buf, c0, r0);
+          }
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {      // free this accumulator buffer in the LEADER (its MMA warp owns the schedule)
+        asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(acc ? tempty_leader1 : tempty_leader0) : "memory");
+      }
+    }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+
+  tc::tc_fence_before();
+  tc::cluster_sync();                          // neither CTA may exit (or free TMEM) while the peer still uses it
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc<2>(tmem_base, 512);
+  }
+}
+
+template <bool kAMN, bool kBMN>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
+  auto kern = gemm2_kernel<kAMN, kBMN>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    attr_set = true;
+  }
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
+  kern<<<2 * clusters, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);
+  return check_launch("gemm2_bf16");
+}
+
+}  // namespace gemm2
+
+// called from dla_gemm_bf16 (gemm.cu)
+int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                   int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream) {
+  using namespace gemm2;
+  CUtensorMap tmA, tmB, tmC;
+  int rc;
+  if (!a_mn) rc = make_tmap_2d_bf16(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
+  else       rc = make_tmap_2d_bf16(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
+  if (rc) return rc;
+  if (!b_mn) rc = make_tmap_2d_bf16(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, BNH);
+  else       rc = make_tmap_2d_bf16(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
+  if (rc) return rc;
+  const int esz = c_fp32 ? 4 : 2;
+  rc = make_tmap_2d(&tmC, C, c_fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, esz, (uint64_t)N,
+                    (uint64_t)M, (uint64_t)ldc, c_fp32 ? 32 : 64, 32);
+  if (rc) return rc;
+  Params p{};
+  p.M = M; p.N = N; p.K = K; p.c_fp32 = c_fp32; p.accumulate = accumulate;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  if (!a_mn && !b_mn) return launch<false, false>(tmA, tmB, tmC, p, stream);
+  if (!a_mn && b_mn) return launch<false, true>(tmA, tmB, tmC, p, stream);
+  if (a_mn && !b_mn) return launch<true, false>(tmA, tmB, tmC, p, stream);
+  return launch<true, true>(tmA, tmB, tmC, p, stream);
+}
+
+}  // namespace dla

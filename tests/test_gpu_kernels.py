@@ -337,3 +337,28 @@ def test_top_p_sampler_kernel(native_lib):
     want = float(sp[b, 0] / sp[b][keep[b]].sum())
     freq = float((draws[b] == top_tok).float().mean())
     assert abs(freq - want) < 0.08, (freq, want)
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (256, 512, 512), (1000, 1030, 520), (4096, 6144, 4096), (520, 264, 304)])
+def test_gemm_2cta_variant(native_lib, M, N, K):
+    """cta_group::2 kernel (256x256 cluster tiles) in all four operand layouts + accumulate epilogues."""
+    from dla_b200.ops import native as N_
+
+    torch.manual_seed(15)
+    a, b = _rand(M, K), _rand(N, K)
+    ref = a.float() @ b.float().t()
+    tol = dict(rtol=2e-2, atol=0.02 * math.sqrt(K))
+    N_.call("dla_gemm_set_variant", 2)
+    try:
+        _close(F.gemm(a, b), ref, what="2cta NT", **tol)
+        _close(F.gemm(a, b.t().contiguous(), b_mn=True), ref, what="2cta NN", **tol)
+        _close(F.gemm(a.t().contiguous(), b, a_mn=True), ref, what="2cta TN", **tol)
+        _close(F.gemm(a.t().contiguous(), b.t().contiguous(), a_mn=True, b_mn=True), ref, what="2cta TT", **tol)
+        out = torch.ones(M, N, device=DEV, dtype=torch.float32)
+        F.gemm(a, b, out=out, accumulate=True)
+        _close(out, ref + 1, what="2cta fp32 accumulate", **tol)
+        outb = torch.ones(M, N, device=DEV, dtype=BF16)
+        F.gemm(a, b, out=outb, accumulate=True)
+        _close(outb, ref + 1, what="2cta bf16 accumulate", rtol=2e-2, atol=0.03 * math.sqrt(K))
+    finally:
+        N_.call("dla_gemm_set_variant", 0)

@@ -58,8 +58,11 @@ def main():
             c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
             flops = 2.0 * M * Nn * K
             t_own = timeit(lambda: F.gemm(a, b, out=c))
+            N.call("dla_gemm_set_variant", 2)
+            t_2cta = timeit(lambda: F.gemm(a, b, out=c))
+            N.call("dla_gemm_set_variant", 0)
             t_lib = timeit(lambda: torch.matmul(a, b.t(), out=c))
-            rec = {"kernel": "gemm_nt", "tag": tag, "M": M, "N": Nn, "K": K, "ms": t_own, "tflops": flops / t_own / 1e9,
+            rec = {"kernel": "gemm_nt", "tag": tag, "M": M, "N": Nn, "K": K, "ms": t_own, "tflops": flops / t_own / 1e9, "tflops_2cta": flops / t_2cta / 1e9,
                    "cublas_ms": t_lib, "cublas_tflops": flops / t_lib / 1e9,
                    "frac_of_measured_peak": flops / t_own / 1e9 / PK["bf16_tflops"]}
             # dgrad (B mn-major) and wgrad (both mn-major) of the same Linear
@@ -68,6 +71,10 @@ def main():
             dw = torch.empty(Nn, K, device=DEV, dtype=torch.bfloat16)
             rec["dgrad_tflops"] = flops / timeit(lambda: F.gemm(dy, b, b_mn=True, out=dx)) / 1e9
             rec["wgrad_tflops"] = flops / timeit(lambda: F.gemm(dy, a, a_mn=True, b_mn=True, out=dw)) / 1e9
+            N.call("dla_gemm_set_variant", 2)
+            rec["dgrad_tflops_2cta"] = flops / timeit(lambda: F.gemm(dy, b, b_mn=True, out=dx)) / 1e9
+            rec["wgrad_tflops_2cta"] = flops / timeit(lambda: F.gemm(dy, a, a_mn=True, b_mn=True, out=dw)) / 1e9
+            N.call("dla_gemm_set_variant", 0)
             out.append(rec)
             print(json.dumps(rec), flush=True)
     if "attn" in which:
