@@ -42,7 +42,8 @@ __device__ __forceinline__ float uniform01(uint64_t seed, uint64_t offset, uint6
 
 __global__ void __launch_bounds__(kThreads)
 sample_kernel(const void* __restrict__ logits, int fp32, int V, int64_t ld, float inv_temp, float top_p, uint64_t seed,
-              uint64_t offset, int64_t* __restrict__ out) {
+              uint64_t offset, const int64_t* __restrict__ offset_dev, int64_t* __restrict__ out) {
+  if (offset_dev != nullptr) offset += (uint64_t)*offset_dev;       // replayed graphs advance the counter on the device
   __shared__ float red[33];
   __shared__ float s_part[kThreads];
   __shared__ int s_pick;
@@ -138,14 +139,13 @@ size_t dla_sampler_scratch_bytes(int B, int V) {
 }
 
 int dla_sample_top_p(const void* logits, int logits_fp32, int B, int V, int64_t ld, float temperature, float top_p,
-                     uint64_t seed, uint64_t offset, void* scratch, int64_t* out, void* stream) {
+                     uint64_t seed, uint64_t offset, const int64_t* offset_dev, int64_t* out, void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
-  (void)scratch;
   DLA_REQUIRE(B > 0 && V > 0 && out != nullptr, DLA_E_BADARG, "sample_top_p: bad shape B=%d V=%d", B, V);
   DLA_REQUIRE(top_p > 0.f, DLA_E_BADARG, "sample_top_p: top_p must be > 0");
   const float inv_temp = temperature > 0.f ? 1.f / temperature : 0.f;
   sampler::sample_kernel<<<B, sampler::kThreads, 0, (cudaStream_t)stream>>>(logits, logits_fp32, V, ld, inv_temp,
-                                                                            top_p > 1.f ? 1.f : top_p, seed, offset, out);
+                                                                            top_p > 1.f ? 1.f : top_p, seed, offset, offset_dev, out);
   return check_launch("sample_top_p");
 }
 

@@ -69,9 +69,47 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         else:
             out.copy_(res.to(out.dtype))
         return out
+    if M <= SKINNY_MAX_ROWS and K % 32 == 0 and not (a_mn or b_mn or accumulate):
+        # decode shapes: bound by the HBM stream of the weight, see csrc/skinny.cu
+        N.call("dla_gemm_skinny_bf16", N.ptr(a), N.ptr(b), N.ptr(out), None, None, M, Nn, K, a.stride(0), b.stride(0),
+               out.stride(0), 0, int(out.dtype == torch.float32), int(_STATIC_WEIGHTS[0]), _s(a))
+        return out
     N.call("dla_gemm_bf16", N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, a.stride(0), b.stride(0), out.stride(0),
            int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), _s(a))
     return out
+
+
+SKINNY_MAX_ROWS = 16                 # above this the 128-row tcgen05 tiles win (profiles/kernels_r1_skinny.jsonl)
+_STATIC_WEIGHTS = [False]
+
+
+class weights_static:
+    """Context: no kernel in the stream writes the weights while it is active (generation, evaluation), so
+    decode GEMMs may start early and prefetch their weight stream (``weights_static`` of dla_gemm_skinny_bf16)."""
+
+    def __enter__(self):
+        self.prev = _STATIC_WEIGHTS[0]
+        _STATIC_WEIGHTS[0] = True
+        return self
+
+    def __exit__(self, *exc):
+        _STATIC_WEIGHTS[0] = self.prev
+        return False
+
+
+def linear_residual(x: torch.Tensor, w: torch.Tensor, resid: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``resid + x @ w^T (+ bias)``; for decode-sized inputs the add rides in the weight-streaming GEMM's epilogue."""
+    x2 = x.reshape(-1, x.shape[-1])
+    M, K = x2.shape
+    r2 = resid.reshape(M, -1)
+    if (x2.is_cuda and not torch.is_grad_enabled() and M <= SKINNY_MAX_ROWS and K % 32 == 0 and x2.dtype == BF16 and w.dtype == BF16
+            and x2.stride(1) == 1 and x2.stride(0) % 8 == 0 and w.stride(1) == 1 and w.stride(0) % 8 == 0 and r2.stride(1) == 1
+            and r2.dtype == BF16 and x2.data_ptr() % 16 == 0 and w.data_ptr() % 16 == 0):
+        out = torch.empty(M, w.shape[0], dtype=BF16, device=x.device)
+        N.call("dla_gemm_skinny_bf16", N.ptr(x2), N.ptr(w), N.ptr(out), N.ptr(bias) if bias is not None else None, N.ptr(r2),
+               M, w.shape[0], K, x2.stride(0), w.stride(0), out.stride(0), r2.stride(0), 0, int(_STATIC_WEIGHTS[0]), _s(x2))
+        return out.view(resid.shape)
+    return resid + linear(x, w, bias)
 
 
 _FALLBACKS: dict = {}

@@ -11,7 +11,7 @@ directly by its continuation, right-padded with ``pad_token_id``.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import List, Optional
+from typing import Callable, List, Optional
 
 import torch
 
@@ -39,9 +39,38 @@ class KVCache:
         self.max_len = max_len
 
 
+@dataclass
+class _DecodeState:
+    logits: torch.Tensor      # [B, V] next-token logits of every row
+    seqs: torch.Tensor        # [B, max_len]
+    lens: torch.Tensor        # [B] int32 valid tokens per row
+    finished: torch.Tensor    # [B] bool
+    nxt: torch.Tensor         # [B] token chosen by the last pick
+    counter: torch.Tensor     # [1] int64 RNG counter, advanced on the device
+
+
+@dataclass
+class _DecodeSession:
+    cache: KVCache
+    st: _DecodeState
+    pick: Callable[[], None]
+    advance: Callable[[], None]
+    graph: Optional["torch.cuda.CUDAGraph"] = None
+
+
+_SEED_BASE = 0x5EED5EED            # kernel-side constant; the per-call seed enters through the device counter
+
+
 class Generator:
-    def __init__(self, model: CausalLM) -> None:
+    def __init__(self, model: CausalLM, use_cuda_graph: bool = True, finish_check_every: int = 8) -> None:
         self.model, self.cfg, self.p = model, model.cfg, model.p
+        self.use_cuda_graph = use_cuda_graph
+        self.finish_check_every = max(1, int(finish_check_every))    # host reads `finished` only this often
+        self._sessions: dict = {}
+
+    def _graphable(self, dev: torch.device) -> bool:
+        """The decode step can be captured when acquiring a unit launches nothing (parameters resident)."""
+        return bool(self.use_cuda_graph and dev.type == "cuda" and getattr(self.p, "resident", True))
 
     # ---- per-layer math with cache ------------------------------------------------------
     def _qkv(self, w: Weights, x: torch.Tensor, positions: torch.Tensor):
@@ -61,12 +90,40 @@ class Generator:
         cfg = self.cfg
         B, T, H = x.shape
         if cfg.arch == "gpt2":
-            x = x + F.linear(attn.reshape(B, T, H), w["wo"], w["bo"])
+            x = F.linear_residual(attn.reshape(B, T, H), w["wo"], x, w["bo"])
             h = F.layernorm(x, w["ln2_w"], w["ln2_b"], cfg.norm_eps)
-            return x + F.linear(F.gelu_bias(F.linear(h, w["w_fc"]), w["b_fc"]), w["w_proj"], w["b_proj"])
+            return F.linear_residual(F.gelu_bias(F.linear(h, w["w_fc"]), w["b_fc"]), w["w_proj"], x, w["b_proj"])
         a = F.linear(attn.reshape(B, T, cfg.q_dim), w["wo"])
         x, h = F.add_rmsnorm(x, a, w["mlp_norm"], cfg.norm_eps)
-        return x + F.linear(F.swiglu(F.linear(h, w["w_gu"])), w["w_down"])
+        return F.linear_residual(F.swiglu(F.linear(h, w["w_gu"])), w["w_down"], x)
+
+    def _fused_decode_ok(self, dev: torch.device, max_len: int) -> bool:
+        cfg = self.cfg
+        g = cfg.num_heads // cfg.num_kv_heads
+        stripes = 256 // (cfg.head_dim // 8) if cfg.head_dim in (64, 128) else 0
+        smem = 4 * (g * cfg.head_dim + g * max_len + stripes * g * cfg.head_dim)
+        return dev.type == "cuda" and cfg.head_dim in (64, 128) and g in (1, 2, 4, 8) and smem <= 220 * 1024
+
+    def _decode_layer_attention(self, w: Weights, x: torch.Tensor, cache: KVCache, layer: int, lens: torch.Tensor) -> torch.Tensor:
+        """Norm + QKV projection of one token per row, then RoPE + cache append + attention in one kernel
+        (``csrc/decode.cu``); ``lens`` already counts the new token.  Returns ``[B, Hq, D]``."""
+        cfg = self.cfg
+        B, _, H = x.shape
+        if cfg.arch == "gpt2":
+            h = F.layernorm(x, w["ln1_w"], w["ln1_b"], cfg.norm_eps)
+            qkv = F.linear(h, w["wqkv"], w["bqkv"]).reshape(B, -1)
+            cos = sin = None
+            rot = 0
+        else:
+            h = F.rmsnorm(x, w["attn_norm"], cfg.norm_eps)
+            qkv = F.linear(h.reshape(B, H), w["wqkv"])
+            rot = cfg.rot_dim or cfg.head_dim
+            cos, sin = F.rope_tables(cfg.max_position_embeddings, rot, cfg.rope_theta, x.device)
+        o = torch.empty(B, cfg.num_heads, cfg.head_dim, dtype=qkv.dtype, device=x.device)
+        N.call("dla_decode_attn_fused", N.ptr(qkv), qkv.stride(0), N.ptr(cache.k[layer]), N.ptr(cache.v[layer]), N.ptr(o), N.ptr(lens),
+               N.ptr(cos) if cos is not None else None, N.ptr(sin) if sin is not None else None, B, cache.max_len, cfg.num_heads,
+               cfg.num_kv_heads, cfg.head_dim, rot, cfg.head_dim ** -0.5, N.stream_ptr(x.device))
+        return o
 
     def _final(self, x: torch.Tensor) -> torch.Tensor:
         w = self.p.acquire("head")
@@ -90,6 +147,68 @@ class Generator:
             return o
         return R.attention(q[:, None], cache.k[layer], cache.v[layer], causal=False, seqlens=lens)[:, 0]
 
+    # ---- decode session -----------------------------------------------------------------
+    def _session(self, key: tuple, B: int, max_len: int, dev: torch.device, dtype: torch.dtype, temp: float, top_p: float,
+                 eos: int, pad: int) -> "_DecodeSession":
+        """Fixed device buffers + the two halves of a decode step for one (batch, length, sampling) signature.
+        Sessions are kept (most recent two) so that repeated rollouts of the same shape — every PPO step —
+        replay the graph captured the first time instead of re-capturing it."""
+        ses = self._sessions.get(key)
+        if ses is not None:
+            return ses
+        cfg = self.cfg
+        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
+        cache = KVCache(cfg, B, max_len, dev, dtype)
+        st = _DecodeState(logits=torch.zeros(B, cfg.vocab_size, dtype=dtype, device=dev),
+                          seqs=torch.full((B, max_len), pad, dtype=torch.long, device=dev),
+                          lens=torch.zeros(B, dtype=torch.int32, device=dev), finished=torch.zeros(B, dtype=torch.bool, device=dev),
+                          nxt=torch.zeros(B, dtype=torch.long, device=dev), counter=torch.zeros(1, dtype=torch.long, device=dev))
+        rows = torch.arange(B, device=dev)
+        fused = self._fused_decode_ok(dev, max_len)
+
+        def pick() -> None:
+            """Sample one token per row and update sequences / lengths / finished flags (no host sync)."""
+            nxt = sample(st.logits, temp, top_p, None, seed=_SEED_BASE, step=0, step_dev=st.counter)
+            nxt = torch.where(st.finished, torch.full_like(nxt, pad), nxt)
+            can = (~st.finished) & (st.lens < max_len)
+            idx = st.lens.long().clamp(max=max_len - 1)
+            st.seqs[rows, idx] = torch.where(can, nxt, st.seqs[rows, idx])
+            st.lens.add_(can.to(torch.int32))
+            st.finished.logical_or_((can & (nxt == eos)) | (st.lens >= max_len))
+            st.nxt.copy_(nxt)
+            st.counter.add_(1)
+
+        def advance() -> None:
+            """One decode forward for the tokens chosen by ``pick`` (position lens-1), refreshing ``st.logits``."""
+            tok_pos = (st.lens - 1).clamp(min=0)
+            x = F.embedding(st.nxt[:, None], self.p.acquire("embed")["tok_emb"], None)
+            if cfg.arch == "gpt2":
+                x = x + self.p.acquire("embed")["pos_emb"][tok_pos.long()][:, None]
+            self.p.release("embed")
+            pos64 = None if fused else tok_pos.long()
+            for i in range(cfg.num_layers):
+                w = self.p.acquire(f"layer.{i}")
+                if fused:
+                    attn = self._decode_layer_attention(w, x, cache, i, st.lens)
+                else:
+                    qkv = self._qkv(w, x, tok_pos[:, None])
+                    cache.k[i, rows, pos64] = qkv[:, 0, Hq:Hq + Hk]
+                    cache.v[i, rows, pos64] = qkv[:, 0, Hq + Hk:]
+                    attn = self._decode_attention(qkv[:, 0, :Hq].contiguous(), cache, i, st.lens)
+                x = self._post_attn(w, x, attn[:, None])
+                self.p.release(f"layer.{i}")
+            st.logits.copy_(self._final(x)[:, 0])
+
+        ses = _DecodeSession(cache=cache, st=st, pick=pick, advance=advance)
+        while len(self._sessions) >= 2:
+            self._sessions.pop(next(iter(self._sessions)))
+        self._sessions[key] = ses
+        return ses
+
+    def reset(self) -> None:
+        """Drop cached decode sessions (KV buffers and captured graphs), e.g. after parameters were re-allocated."""
+        self._sessions.clear()
+
     # ---- public ------------------------------------------------------------------------
     @torch.no_grad()
     def generate(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, max_new_tokens: int = 256,
@@ -107,13 +226,66 @@ class Generator:
         if cfg.arch == "gpt2":
             max_len = min(max_len, cfg.max_position_embeddings)
         dtype = self.p.acquire("embed")["tok_emb"].dtype
-        cache = KVCache(cfg, B, max_len, dev, dtype)
-        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
-        gen = torch.Generator(device=dev)
+        temp = float(temperature) if do_sample else 0.0
         seed = seed if seed is not None else int(torch.randint(0, 2**31 - 1, (1,)).item())
-        gen.manual_seed(seed)
+        if dev.type != "cuda":
+            return self._generate_host(input_ids, attention_mask, plen, max_len, max_new_tokens, temp, top_p, eos, pad, seed)
+        ses = self._session((B, max_len, str(dev), dtype, temp, float(top_p), int(eos), int(pad)), B, max_len, dev, dtype, temp,
+                            float(top_p), int(eos), int(pad))
+        cache, st = ses.cache, ses.st
+        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
 
         # ---- prefill: full causal attention over the (right-padded) prompts, filling the cache
+        logits = self._prefill(input_ids, plen, cache)
+        st.logits.copy_(logits)
+        st.seqs.fill_(pad)
+        st.seqs[:, :Tp] = torch.where(attention_mask.bool(), input_ids, torch.full_like(input_ids, pad))
+        st.lens.copy_(plen)
+        st.finished.zero_()
+        st.counter.fill_((int(seed) & 0x7FFFFFFF) << 24)     # the seed selects the stream; one count per decoded token
+        steps = min(max_new_tokens, max_len - int(plen.min().item()))
+
+        done = 0
+        with F.weights_static():      # nothing in this stream writes the weights until generation returns
+            if steps > 0:
+                ses.pick()
+                done = 1
+            if ses.graph is None and self._graphable(dev) and steps > 4:
+                # one eager token first (work areas and device binding exist before capture), then capture
+                # "forward + pick" once: ~12 launches per layer collapse into one graph launch per token
+                ses.advance()
+                ses.pick()
+                done = 2
+                ses.graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(ses.graph):
+                    ses.advance()
+                    ses.pick()
+                # capture only records; the state is untouched until the first replay
+            use_graph = ses.graph is not None and self.use_cuda_graph
+            while done < steps:
+                if use_graph:
+                    ses.graph.replay()
+                else:
+                    ses.advance()
+                    ses.pick()
+                done += 1
+                if done % self.finish_check_every == 0 and done < steps and bool(st.finished.all()):
+                    break
+        lens = st.lens.clone()
+        L = int(lens.max().item())
+        seqs = st.seqs[:, :L].clone()
+        ar = torch.arange(L, device=dev)[None]
+        amask = (ar < lens[:, None]).long()
+        rmask = ((ar >= plen[:, None]) & (ar < lens[:, None])).long()
+        return GenerationOutput(seqs, amask, plen.long(), rmask, lens.long())
+
+    def _prefill(self, input_ids: torch.Tensor, plen: torch.Tensor, cache: KVCache) -> torch.Tensor:
+        """Full causal forward over the right-padded prompts; fills ``cache[:, :, :Tp]`` and returns the logits
+        of every row's last prompt token ``[B, V]``."""
+        cfg = self.cfg
+        dev = input_ids.device
+        B, Tp = input_ids.shape
+        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
         pos = torch.arange(Tp, device=dev, dtype=torch.int32).expand(B, Tp)
         x = F.embedding(input_ids, self.p.acquire("embed")["tok_emb"], self.p.acquire("embed").get("pos_emb"))
         self.p.release("embed")
@@ -127,8 +299,19 @@ class Generator:
             x = self._post_attn(w, x, attn)
             self.p.release(f"layer.{i}")
         last = x[torch.arange(B, device=dev), (plen - 1).long().clamp(min=0)].unsqueeze(1)      # [B,1,H]
-        logits = self._final(last)[:, 0]
+        return self._final(last)[:, 0]
 
+    def _generate_host(self, input_ids, attention_mask, plen, max_len, max_new_tokens, temp, top_p, eos, pad, seed) -> GenerationOutput:
+        """CPU restatement of the same loop (tests, tiny models): PyTorch ops, torch.Generator sampling."""
+        cfg = self.cfg
+        dev = input_ids.device
+        B, Tp = input_ids.shape
+        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
+        dtype = self.p.acquire("embed")["tok_emb"].dtype
+        cache = KVCache(cfg, B, max_len, dev, dtype)
+        gen = torch.Generator(device=dev)
+        gen.manual_seed(seed)
+        logits = self._prefill(input_ids, plen, cache)
         seqs = torch.full((B, max_len), pad, dtype=torch.long, device=dev)
         seqs[:, :Tp] = torch.where(attention_mask.bool(), input_ids, torch.full_like(input_ids, pad))
         lens = plen.clone()
@@ -136,7 +319,7 @@ class Generator:
         rows = torch.arange(B, device=dev)
         steps = min(max_new_tokens, max_len - int(plen.min().item()))
         for step in range(steps):
-            nxt = sample(logits, temperature if do_sample else 0.0, top_p, gen, seed=seed, step=step)
+            nxt = sample(logits, temp, top_p, gen, seed=seed, step=step)
             nxt = torch.where(finished, torch.full_like(nxt, pad), nxt)
             can = (~finished) & (lens < max_len)
             idx = lens.long().clamp(max=max_len - 1)
@@ -146,7 +329,6 @@ class Generator:
             finished = finished | newly | (lens >= max_len)
             if step == steps - 1 or bool(finished.all()):
                 break
-            # ---- decode one token per row at position lens-1
             tok_pos = (lens - 1).clamp(min=0)
             x = F.embedding(nxt[:, None], self.p.acquire("embed")["tok_emb"], None)
             if cfg.arch == "gpt2":
@@ -170,18 +352,18 @@ class Generator:
 
 
 def sample(logits: torch.Tensor, temperature: float, top_p: float, generator: Optional[torch.Generator] = None,
-           seed: int = 0, step: int = 0) -> torch.Tensor:
+           seed: int = 0, step: int = 0, step_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Next-token choice on the device: greedy when ``temperature <= 0`` else nucleus sampling.  CUDA runs
     the fused temperature + top-p + multinomial kernel (``csrc/sampler.cu``, counter-based RNG keyed by
-    ``seed``/``step``); CPU runs the sort-based PyTorch restatement."""
+    ``seed``/``step`` plus the device counter ``step_dev`` when given); CPU runs the sort-based PyTorch restatement."""
     if logits.is_cuda:
         lg = logits if logits.is_contiguous() else logits.contiguous()
         if lg.dtype not in (torch.float32, torch.bfloat16):
             lg = lg.float()
         out = torch.empty(lg.shape[0], dtype=torch.int64, device=lg.device)
         N.call("dla_sample_top_p", N.ptr(lg), int(lg.dtype == torch.float32), lg.shape[0], lg.shape[1], lg.stride(0),
-               float(temperature), float(min(max(top_p, 1e-6), 1.0)), int(seed) & 0xFFFFFFFFFFFFFFFF, int(step), None,
-               N.ptr(out), N.stream_ptr(lg.device))
+               float(temperature), float(min(max(top_p, 1e-6), 1.0)), int(seed) & 0xFFFFFFFFFFFFFFFF, int(step),
+               N.ptr(step_dev) if step_dev is not None else None, N.ptr(out), N.stream_ptr(lg.device))
         return out
     if temperature <= 0:
         return logits.argmax(-1)

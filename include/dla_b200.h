@@ -182,11 +182,34 @@ int dla_attn_decode(const void* q, const void* kcache, const void* vcache, void*
                     const int32_t* lens, int B, int S_max, int Hq, int Hk, int D, float scale,
                     void* stream);
 
+/* ---------------------------------------------------------------- decode (weight-streaming) GEMM */
+/* y[M,N] = x[M,K] @ w[N,K]^T (+ bias[N]) (+ residual[M,N]) for M <= dla_gemm_skinny_max_rows() (32): grid over N,
+ * K split across the warps of a CTA, mma.sync on 16-byte global loads; bound by the HBM stream of w.  K % 32 == 0,
+ * row pitches multiples of 8 elements, 16-byte aligned bases.  weights_static != 0 launches with programmatic
+ * stream serialization: the grid may start before its predecessor ends and prefetches w ahead of
+ * griddepcontrol.wait — only legal when no earlier kernel in the stream writes w (decode, not training).
+ * R: per-token nn.Linear inside generate(), R/src/training/train_rlhf.py:123-124. */
+int dla_gemm_skinny_bf16(const void* x, const void* w, void* y, const void* bias, const void* residual, int M,
+                         int N, int K, int64_t ldx, int64_t ldw, int64_t ldy, int64_t ldr, int out_fp32,
+                         int weights_static, void* stream);
+int dla_gemm_skinny_max_rows(void);
+
+/* One-token decode attention fused with RoPE and the KV-cache append (csrc/decode.cu): qkv is the fresh
+ * [B, (Hq+2Hk)*D] projection of one token per sequence (row pitch qkv_stride elements); lens[b] counts the valid
+ * positions INCLUDING this token.  The kernel rotates q and k (rot_dim leading dims of each head, table
+ * cos_t/sin_t [max_pos, rot_dim/2]; rot_dim 0 = no RoPE), writes k/v at position lens[b]-1 of the
+ * [B, S_max, Hk, D] caches and attends over lens[b] positions; o is [B, Hq, D].  D in {64,128}, Hq/Hk in {1,2,4,8}.
+ * R: DynamicCache.update + apply_rotary_pos_emb + SDPA per generated token, R/src/training/train_rlhf.py:123-124. */
+int dla_decode_attn_fused(void* qkv, int64_t qkv_stride, void* kcache, void* vcache, void* o, const int32_t* lens,
+                          const float* cos_t, const float* sin_t, int B, int S_max, int Hq, int Hk, int D,
+                          int rot_dim, float scale, void* stream);
+
 /* ---------------------------------------------------------------- sampling (K16) */
 /* Per-row temperature + top-p + multinomial on fp32/bf16 logits [B,V]; writes int64 token ids.
- * scratch: dla_sampler_scratch_bytes(B, V). seed/offset: Philox-style counter RNG. */
+ * seed/offset: counter RNG; offset_dev (nullable) is a device int64 added to offset inside the kernel, so a
+ * captured decode graph draws fresh numbers on every replay.  No work area is needed. */
 int dla_sample_top_p(const void* logits, int logits_fp32, int B, int V, int64_t ld, float temperature,
-                     float top_p, uint64_t seed, uint64_t offset, void* scratch, int64_t* out,
+                     float top_p, uint64_t seed, uint64_t offset, const int64_t* offset_dev, int64_t* out,
                      void* stream);
 size_t dla_sampler_scratch_bytes(int B, int V);
 

@@ -309,6 +309,39 @@ def test_attention_decode(native_lib):
     _close(o, ref, what="decode attention")
 
 
+@pytest.mark.parametrize("Hq,Hk,D,rot", [(8, 2, 128, 128), (4, 4, 64, 32), (8, 1, 128, 128), (6, 3, 64, 0)])
+def test_decode_attention_fused_rope_cache_append(native_lib, Hq, Hk, D, rot):
+    """csrc/decode.cu: RoPE + cache append + one-token attention against the fp32 composition of the same steps."""
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(17)
+    B, S = 4, 90
+    lens = torch.tensor([1, 17, 90, 64], device=DEV, dtype=torch.int32)
+    qkv = _rand(B, (Hq + 2 * Hk) * D)
+    kc, vc = _rand(B, S, Hk, D), _rand(B, S, Hk, D)
+    kc0, vc0 = kc.clone(), vc.clone()
+    theta = 10000.0
+    pos = (lens - 1).long()
+    q, k, v = qkv.view(B, Hq + 2 * Hk, D).split([Hq, Hk, Hk], dim=1)
+    if rot:
+        cos, sin = F.rope_tables(128, rot, theta, torch.device(DEV))
+        qr = R.rope(q[:, None], pos[:, None], theta, rot)[:, 0]
+        kr = R.rope(k[:, None], pos[:, None], theta, rot)[:, 0]
+    else:
+        cos = sin = None
+        qr, kr = q, k
+    kref, vref = kc0.clone(), vc0.clone()
+    kref[torch.arange(B), pos] = kr
+    vref[torch.arange(B), pos] = v
+    ref = R.attention(qr[:, None], kref, vref, causal=False, seqlens=lens)[:, 0]
+    o = torch.empty(B, Hq, D, device=DEV, dtype=BF16)
+    N.call("dla_decode_attn_fused", N.ptr(qkv), qkv.stride(0), N.ptr(kc), N.ptr(vc), N.ptr(o), N.ptr(lens),
+           N.ptr(cos) if rot else None, N.ptr(sin) if rot else None, B, S, Hq, Hk, D, rot, 1 / math.sqrt(D), N.stream_ptr())
+    _close(o, ref, what="fused decode attention")
+    _close(kc, kref, atol=1e-2, what="appended k row (and untouched rest of the cache)")
+    assert torch.equal(vc, vref), "v row must be copied verbatim and the rest of the cache untouched"
+
+
 def test_top_p_sampler_kernel(native_lib):
     from dla_b200.rollout import sample
 
@@ -362,3 +395,28 @@ def test_gemm_2cta_variant(native_lib, M, N, K):
         _close(outb, ref + 1, what="2cta bf16 accumulate", rtol=2e-2, atol=0.03 * math.sqrt(K))
     finally:
         N_.call("dla_gemm_set_variant", 0)
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 4096, 4096), (8, 6144, 4096), (8, 4096, 14336), (13, 50257, 768), (16, 28672, 4096),
+                                   (32, 1000, 96), (5, 24, 32)])
+def test_gemm_skinny_decode_shapes(native_lib, M, N, K):
+    """Weight-streaming decode GEMM (csrc/skinny.cu) against fp32 matmul, bf16 and fp32 outputs, with bias."""
+    from dla_b200.ops import native as Nn
+
+    torch.manual_seed(9)
+    a, b = _rand(M, K), _rand(N, K)
+    ref = a.float() @ b.float().t()
+    for dt in (torch.bfloat16, torch.float32):
+        c = F.gemm(a, b, out_dtype=dt)          # M <= 32 dispatches to the skinny kernel
+        _close(c, ref, rtol=2e-2, atol=0.02 * math.sqrt(K), what=f"skinny {M}x{N}x{K} {dt}")
+    bias = _rand(N)
+    y = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    res = _rand(M, N)
+    for early in (0, 1):        # 1 = programmatic dependent launch (weight prefetch ahead of griddepcontrol.wait)
+        y.zero_()
+        Nn.call("dla_gemm_skinny_bf16", Nn.ptr(a), Nn.ptr(b), Nn.ptr(y), Nn.ptr(bias), Nn.ptr(res), M, N, K, a.stride(0), b.stride(0),
+                y.stride(0), res.stride(0), 0, early, Nn.stream_ptr())
+        _close(y, ref + bias.float() + res.float(), rtol=2e-2, atol=0.02 * math.sqrt(K), what=f"skinny + bias + residual (early={early})")
+    # the tensor-core tile kernel must agree on the same operands (33 rows take the tcgen05 path)
+    a33 = torch.cat([a, a[:1].expand(33 - M, K)], 0).contiguous()
+    _close(F.gemm(a33, b)[:M], ref, rtol=2e-2, atol=0.02 * math.sqrt(K), what="tile kernel on the same operands")

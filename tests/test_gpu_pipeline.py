@@ -32,9 +32,18 @@ def test_kv_cache_rollout_consistent_with_full_forward(native_lib, ctx, name):
         for t in range(p, L):
             row = logits[r, t - 1]
             assert row[out.sequences[r, t]] >= row.max() - 0.08, (name, r, t)
-    s1 = Generator(b.model).generate(ids, mask, max_new_tokens=6, do_sample=True, temperature=0.9, top_p=0.8, seed=3, eos_token_id=-1)
-    s2 = Generator(b.model).generate(ids, mask, max_new_tokens=6, do_sample=True, temperature=0.9, top_p=0.8, seed=3, eos_token_id=-1)
-    assert torch.equal(s1.sequences, s2.sequences)
+    # the captured decode graph must reproduce the eager launch sequence token for token
+    eager = Generator(b.model, use_cuda_graph=False).generate(ids, mask, max_new_tokens=8, do_sample=False, eos_token_id=-1, pad_token_id=0)
+    assert torch.equal(eager.sequences, out.sequences) and torch.equal(eager.lengths, out.lengths)
+    e1 = Generator(b.model, use_cuda_graph=False).generate(ids, mask, max_new_tokens=6, do_sample=True, temperature=0.9, top_p=0.8, seed=3,
+                                                           eos_token_id=-1)
+    g = Generator(b.model)        # second and third call replay the graph captured by the first
+    s1 = g.generate(ids, mask, max_new_tokens=6, do_sample=True, temperature=0.9, top_p=0.8, seed=3, eos_token_id=-1)
+    s2 = g.generate(ids, mask, max_new_tokens=6, do_sample=True, temperature=0.9, top_p=0.8, seed=3, eos_token_id=-1)
+    s3 = g.generate(ids, mask, max_new_tokens=6, do_sample=True, temperature=0.9, top_p=0.8, seed=4, eos_token_id=-1)
+    assert len(g._sessions) == 1 and next(iter(g._sessions.values())).graph is not None
+    assert not torch.equal(s1.sequences, s3.sequences), "a different seed must give a different sample"
+    assert torch.equal(s1.sequences, s2.sequences) and torch.equal(s1.sequences, e1.sequences)
 
 
 def test_sft_reward_distill_steps_learn(native_lib, ctx):

@@ -3,6 +3,8 @@
 
   sft      Llama-3-8B SFT, 4096-token sequences (config 2): tokens/s of fwd + bwd + AdamW
   latency  prefill latency grid of the reference's eval (config 6): B in {1,4,8} x S in {256,512,1024}
+  decode   KV-cache generation (PPO rollout / teacher sampling / eval): ms per token, own Generator (eager and
+           CUDA-graph) vs transformers generate()
   ppo      Llama-3-8B RLHF step (config 4): KV-cache rollout tokens/s, scoring + update time
 
     python tools/bench_configs.py sft|latency|ppo [--model llama3-8b] [--impl own|reference]
@@ -25,7 +27,7 @@ from dla_b200.config import HardwarePlan  # noqa: E402
 from dla_b200.parallel.pg import init_distributed  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("what", choices=["sft", "latency", "ppo"])
+ap.add_argument("what", choices=["sft", "latency", "ppo", "decode"])
 ap.add_argument("--model", default="llama3-8b")
 ap.add_argument("--impl", default="own", choices=["own", "reference"])
 ap.add_argument("--steps", type=int, default=4)
@@ -144,6 +146,35 @@ elif args.what == "latency":
                 ms = timed(lambda: fwd(ids, mask), 20, 5)          # R/config/eval_config.yaml:28-29
                 emit({"config": "prefill_latency", "batch_size": B, "seq_length": S, "latency_ms": ms,
                       "tokens_per_second": B * S / ms * 1e3})
+
+elif args.what == "decode":
+    B, Tp, Tn = 8, 256, args.new_tokens
+    if args.impl == "own":
+        from dla_b200.models.factory import load_causal_lm
+        from dla_b200.rollout import Generator
+
+        b = load_causal_lm(args.model, ctx, trainable=False, gradient_checkpointing=False, name="gen")
+        V = b.config.vocab_size
+        ids = torch.randint(4, V, (B, Tp), device=dev)
+        variants = {"graph": Generator(b.model), "eager": Generator(b.model, use_cuda_graph=False)}
+        runs = {k: (lambda g=g, n=Tn: g.generate(ids, torch.ones_like(ids), max_new_tokens=n, do_sample=True, temperature=0.7,
+                                                 top_p=0.9, seed=1, eos_token_id=-1, pad_token_id=0)) for k, g in variants.items()}
+        pre = lambda: variants["eager"].generate(ids, torch.ones_like(ids), max_new_tokens=1, do_sample=True, temperature=0.7,
+                                                 top_p=0.9, seed=1, eos_token_id=-1, pad_token_id=0)
+    else:
+        m = hf_model(False)
+        V = m.config.vocab_size
+        ids = torch.randint(4, V, (B, Tp), device=dev)
+        kw = dict(do_sample=True, temperature=0.7, top_p=0.9, pad_token_id=0, eos_token_id=None)   # R/config/rlhf_config.yaml:19-24
+        runs = {"hf_generate": lambda: m.generate(input_ids=ids, attention_mask=torch.ones_like(ids), max_new_tokens=Tn,
+                                                  min_new_tokens=Tn, **kw)}
+        pre = lambda: m.generate(input_ids=ids, attention_mask=torch.ones_like(ids), max_new_tokens=1, min_new_tokens=1, **kw)
+    with torch.no_grad():
+        t_pre = timed(pre, 3, 2)
+        for name, fn in runs.items():
+            ms = timed(fn, 3, 2)
+            emit({"config": "decode", "variant": name, "batch": B, "prompt_len": Tp, "new_tokens": Tn, "total_ms": ms, "prefill_ms": t_pre,
+                  "ms_per_token": (ms - t_pre) / max(Tn - 1, 1), "tokens_per_s": B * Tn * W / ms * 1e3})
 
 elif args.what == "ppo":
     from dla_b200.algo import reinforce_step, sequence_logprobs

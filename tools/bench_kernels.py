@@ -77,6 +77,19 @@ def main():
             N.call("dla_gemm_set_variant", 0)
             out.append(rec)
             print(json.dumps(rec), flush=True)
+    if "skinny" in which:
+        for M in (1, 8, 16):
+            for Nn, K, tag in [(6144, 4096, "qkv"), (4096, 4096, "wo"), (28672, 4096, "gate_up"), (4096, 14336, "down"), (128256, 4096, "lm_head")]:
+                a, b = rnd(M, K), rnd(Nn, K)
+                c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+                byt = 2.0 * (Nn * K + M * K + M * Nn)
+                t_own = timeit(lambda: F.gemm(a, b, out=c))
+                t_tile = timeit(lambda: N.call("dla_gemm_bf16", N.ptr(a), N.ptr(b), N.ptr(c), M, Nn, K, K, K, Nn, 0, 0, 0, 0, N.stream_ptr()))
+                t_lib = timeit(lambda: torch.matmul(a, b.t(), out=c))
+                rec = {"kernel": "gemm_skinny", "tag": tag, "M": M, "N": Nn, "K": K, "ms": t_own, "gbs": byt / t_own / 1e6,
+                       "frac_hbm": byt / t_own / 1e6 / PK["hbm_gbs"], "tile_kernel_ms": t_tile, "cublas_ms": t_lib}
+                out.append(rec)
+                print(json.dumps(rec), flush=True)
     if "attn" in which:
         for B, T, Hq, Hk, D in [(8, 1024, 32, 8, 128), (2, 4096, 32, 8, 128)]:
             qkv = rnd(B, T, Hq + 2 * Hk, D).requires_grad_()
