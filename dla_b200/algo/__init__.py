@@ -99,26 +99,17 @@ def reward_step(rm: Any, batch: Dict[str, Dict[str, torch.Tensor]], concat: bool
 
 def reinforce_step(policy_logp: torch.Tensor, ref_logp: torch.Tensor, scores: torch.Tensor, kl_coef: float,
                    baseline: Optional[torch.Tensor] = None):
-    """Sequence-level REINFORCE with batch-mean baseline and KL penalty — exactly the reference's update."""
-    return R.reinforce_loss(policy_logp, ref_logp, scores, kl_coef, baseline)
+    """Sequence-level REINFORCE with batch-mean baseline and KL penalty — exactly the reference's update; one
+    kernel on CUDA (``csrc/rl.cu``)."""
+    return F.reinforce_loss(policy_logp, ref_logp, scores, kl_coef, baseline)
 
 
 def ppo_losses(new_logp: torch.Tensor, old_logp: torch.Tensor, advantages: torch.Tensor, values: torch.Tensor,
                old_values: torch.Tensor, returns: torch.Tensor, mask: torch.Tensor, clip: float = 0.2,
                vclip: float = 0.2, vf_coef: float = 0.5):
-    """Token-level clipped PPO objective + clipped value loss; returns (loss, stats)."""
-    m = mask.to(new_logp.dtype)
-    denom = m.sum().clamp(min=1)
-    ratio = torch.exp(new_logp - old_logp)
-    pg = torch.max(-advantages * ratio, -advantages * ratio.clamp(1 - clip, 1 + clip))
-    pg_loss = (pg * m).sum() / denom
-    vclipped = old_values + (values - old_values).clamp(-vclip, vclip)
-    vf = 0.5 * torch.max((values - returns) ** 2, (vclipped - returns) ** 2)
-    vf_loss = (vf * m).sum() / denom
-    approx_kl = (0.5 * ((new_logp - old_logp) ** 2) * m).sum() / denom
-    clipfrac = (((ratio - 1).abs() > clip).to(m.dtype) * m).sum() / denom
-    return pg_loss + vf_coef * vf_loss, {"pg_loss": pg_loss.detach(), "vf_loss": vf_loss.detach(),
-                                         "approx_kl": approx_kl.detach(), "clipfrac": clipfrac.detach()}
+    """Token-level clipped PPO objective + clipped value loss; returns (loss, stats).  One kernel on CUDA."""
+    loss, st = F.ppo_loss(new_logp, old_logp, advantages, values, old_values, returns, mask, clip, vclip, vf_coef)
+    return loss, {"pg_loss": st[0], "vf_loss": st[1], "approx_kl": st[2], "clipfrac": st[3]}
 
 
 class _ChunkedDistillKL(torch.autograd.Function):
@@ -135,11 +126,17 @@ class _ChunkedDistillKL(torch.autograd.Function):
         total = torch.zeros((), dtype=torch.float32, device=hs.device)
         for s in range(0, M, chunk):
             e = min(s + chunk, M)
-            sl = F.gemm(hs[s:e], ws, out_dtype=torch.float32) if hs.is_cuda else hs[s:e].float() @ ws.float().t()
+            if hs.is_cuda:
+                sl = F.gemm(hs[s:e], ws, out_dtype=torch.float32)
+                tls = [F.gemm(h_t[s:e], w_t, out_dtype=torch.float32) for h_t, w_t in zip(ht, wt)]
+                kl, _ = F.distill_kl_rows(sl, tls, None, temperature, want_kl=True, want_grad=False)
+                total = total + (kl * m[s:e]).sum()
+                continue
+            sl = hs[s:e].float() @ ws.float().t()
             slp = torch.log_softmax(sl / temperature, -1)
             tp = None
             for h_t, w_t in zip(ht, wt):
-                tl = F.gemm(h_t[s:e], w_t, out_dtype=torch.float32) if hs.is_cuda else h_t[s:e].float() @ w_t.float().t()
+                tl = h_t[s:e].float() @ w_t.float().t()
                 pr = torch.softmax(tl / temperature, -1)
                 tp = pr if tp is None else tp + pr
             tp = tp / len(ht)
@@ -162,21 +159,24 @@ class _ChunkedDistillKL(torch.autograd.Function):
         wtgt = slot if slot is not None else dw
         for s in range(0, M, chunk):
             e = min(s + chunk, M)
-            sl = F.gemm(hs[s:e], ws, out_dtype=torch.float32) if hs.is_cuda else hs[s:e].float() @ ws.float().t()
+            if hs.is_cuda:
+                sl = F.gemm(hs[s:e], ws, out_dtype=torch.float32)
+                tls = [F.gemm(h_t[s:e], w_t, out_dtype=torch.float32) for h_t, w_t in zip(ht, wt)]
+                _, dl = F.distill_kl_rows(sl, tls, m[s:e] / denom * g, temperature, want_kl=False, want_grad=True)
+                F.gemm(dl, ws, b_mn=True, out=dh[s:e])
+                F.gemm(dl, hs[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=True)
+                continue
+            sl = hs[s:e].float() @ ws.float().t()
             sp = torch.softmax(sl / temperature, -1)
             tp = None
             for h_t, w_t in zip(ht, wt):
-                tl = F.gemm(h_t[s:e], w_t, out_dtype=torch.float32) if hs.is_cuda else h_t[s:e].float() @ w_t.float().t()
+                tl = h_t[s:e].float() @ w_t.float().t()
                 pr = torch.softmax(tl / temperature, -1)
                 tp = pr if tp is None else tp + pr
             tp = tp / len(ht)
             dl = ((sp - tp) * (m[s:e] / denom * g / temperature)[:, None]).to(hs.dtype)
-            if hs.is_cuda:
-                F.gemm(dl, ws, b_mn=True, out=dh[s:e])
-                F.gemm(dl, hs[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=True)
-            else:
-                dh[s:e] = dl @ ws
-                wtgt.add_((dl.t() @ hs[s:e]).to(wtgt.dtype))
+            dh[s:e] = dl @ ws
+            wtgt.add_((dl.t() @ hs[s:e]).to(wtgt.dtype))
         return (dh, dw, None, None, None) + (None,) * len(teachers)
 
 

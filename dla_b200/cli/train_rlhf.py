@@ -151,11 +151,7 @@ def _ppo_update(loop, policy, vhead, seqs, amask, rmask, ref_tok_logp, scores, p
         rewards = -kl_coef * kl_tok
         last = (rmask.cumsum(1) * rmask).argmax(1).clamp(min=1) - 1
         rewards[torch.arange(seqs.shape[0], device=seqs.device), last] += scores
-        adv, ret = R.gae(rewards, old_values * m, m, gamma, lam)
-        denom = m.sum().clamp(min=1)
-        mean = (adv * m).sum() / denom
-        std = (((adv - mean) ** 2 * m).sum() / denom).sqrt().clamp(min=1e-6)
-        adv = (adv - mean) / std * m
+        adv, ret = F.gae(rewards, old_values * m, m, gamma, lam, whiten=True)      # one launch: scan + whitening
     info.update(kl=(kl_tok.sum(1) / m.sum(1).clamp(min=1)).mean(), reward=rewards.sum(1).mean(), score=scores.mean())
     B = seqs.shape[0]
     loss = torch.zeros((), device=seqs.device)

@@ -13,6 +13,7 @@ from typing import List, Literal, Optional
 import torch
 
 from dla_b200.models.config import ModelConfig
+from dla_b200.ops import functional as F
 from dla_b200.models.transformer import CausalLM, ParamProvider, ParamSpec, UnitSpec, Weights, build_units, run_unit
 
 Pooling = Literal["last_token", "mean"]
@@ -54,10 +55,7 @@ class RewardModel:
         return self.train(False)
 
     def _head(self, w: Weights, hidden: torch.Tensor, attention_mask: torch.Tensor, keep: Optional[torch.Tensor]) -> torch.Tensor:
-        pooled = (pool_last_token if self.pooling == "last_token" else pool_mean)(hidden, attention_mask).float()
-        if keep is not None:
-            pooled = pooled * keep
-        return (pooled @ w["score_w"].float().t()).squeeze(-1) + w["score_b"].float()
+        return F.scalar_head(hidden, attention_mask, w["score_w"], w["score_b"], keep, self.pooling)
 
     def __call__(self, input_ids: torch.Tensor, attention_mask: torch.Tensor) -> torch.Tensor:
         hidden = self.backbone.hidden(input_ids, attention_mask)
@@ -78,7 +76,7 @@ class ValueHead:
 
     @staticmethod
     def _fn(w: Weights, hidden: torch.Tensor) -> torch.Tensor:
-        return (hidden.float() @ w["value_w"].float().t()).squeeze(-1) + w["value_b"].float()
+        return F.scalar_head(hidden, None, w["value_w"], w["value_b"], None, "token")
 
     def __call__(self, hidden: torch.Tensor) -> torch.Tensor:
         return run_unit(self.p, "value_head", self._fn, hidden)

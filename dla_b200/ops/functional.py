@@ -669,3 +669,162 @@ def pairwise_loss(chosen: torch.Tensor, rejected: torch.Tensor, scale: Optional[
     if not chosen.is_cuda:
         return R.pairwise_loss(chosen, rejected) * (scale * B), (chosen > rejected).float().sum() * scale
     return _PairwiseLoss.apply(chosen, rejected, scale)
+
+
+# =======================================================================================
+# scalar heads (reward / value), RL objectives, distillation KL
+# =======================================================================================
+
+HEAD_MODES = {"last_token": 0, "mean": 1, "token": 2}
+
+
+def _grad_to(param: torch.Tensor, g32: torch.Tensor) -> Optional[torch.Tensor]:
+    """Route an fp32 parameter gradient: into the engine's bucket view when the parameter has one."""
+    slot = getattr(param, "_grad_slot", None)
+    if slot is not None:
+        slot.add_(g32.view_as(slot).to(slot.dtype))
+        return None
+    return g32.view_as(param).to(param.dtype)
+
+
+class _ScalarHead(Function):
+    @staticmethod
+    def forward(ctx, hidden, mask, w, bias, keep, mode):
+        B, T, H = hidden.shape
+        hidden = _c(hidden)
+        mask = _c(mask.to(torch.int64)) if mask is not None else None
+        keep = _c(keep.float()) if keep is not None else None
+        out = torch.empty((B, T) if mode == 2 else (B,), dtype=torch.float32, device=hidden.device)
+        N.call("dla_scalar_head_fwd", N.ptr(hidden), N.ptr(mask) if mask is not None else None, N.ptr(w),
+               N.ptr(bias) if bias is not None else None, N.ptr(keep) if keep is not None else None, N.ptr(out), B, T, H, mode,
+               _s(hidden))
+        ctx.save_for_backward(hidden, mask, w, keep)
+        ctx.refs = (w, bias)
+        ctx.mode = mode
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        hidden, mask, w, keep = ctx.saved_tensors
+        wref, bref = ctx.refs
+        B, T, H = hidden.shape
+        dout = _c(dout.float())
+        dh = torch.empty_like(hidden) if ctx.needs_input_grad[0] else None
+        need_w = ctx.needs_input_grad[2]
+        need_b = bref is not None and ctx.needs_input_grad[3]
+        dw32 = torch.zeros(H, dtype=torch.float32, device=hidden.device) if need_w else None
+        db32 = torch.zeros(1, dtype=torch.float32, device=hidden.device) if need_b else None
+        N.call("dla_scalar_head_bwd", N.ptr(hidden), N.ptr(mask) if mask is not None else None, N.ptr(w),
+               N.ptr(keep) if keep is not None else None, N.ptr(dout), N.ptr(dh) if dh is not None else None,
+               N.ptr(dw32) if need_w else None, N.ptr(db32) if need_b else None, B, T, H, ctx.mode, _s(hidden))
+        dw = _grad_to(wref, dw32) if need_w else None
+        db = _grad_to(bref, db32) if need_b else None
+        return dh, None, dw, db, None, None
+
+
+def scalar_head(hidden: torch.Tensor, mask: Optional[torch.Tensor], w: torch.Tensor, bias: Optional[torch.Tensor],
+                keep: Optional[torch.Tensor] = None, mode: str = "last_token") -> torch.Tensor:
+    """Reward head (``mode`` ``last_token`` / ``mean`` -> ``[B]``) or value head (``token`` -> ``[B, T]``), fp32 out.
+    ``w`` is the ``[1, H]`` (or ``[H]``) row of ``Linear(H, 1)``; ``keep`` the scaled dropout mask ``[B, H]``."""
+    if not hidden.is_cuda:
+        return R.scalar_head(hidden, mask, w, bias, keep, mode)
+    _check_bf16(hidden, w)
+    return _ScalarHead.apply(hidden, mask, w, bias, keep, HEAD_MODES[mode])
+
+
+class _Reinforce(Function):
+    @staticmethod
+    def forward(ctx, pol, ref, score, kl_coef, baseline):
+        B = pol.numel()
+        pol, ref, score = (_c(t.float()) for t in (pol, ref, score))
+        base = _c(baseline.float().reshape(1)) if baseline is not None else None
+        out = torch.empty(3, dtype=torch.float32, device=pol.device)
+        kl, rew, dpol = (torch.empty(B, dtype=torch.float32, device=pol.device) for _ in range(3))
+        N.call("dla_reinforce_loss", N.ptr(pol), N.ptr(ref), N.ptr(score), B, float(kl_coef), N.ptr(base) if base is not None else None,
+               N.ptr(out), N.ptr(kl), N.ptr(rew), N.ptr(dpol), _s(pol))
+        ctx.save_for_backward(dpol)
+        ctx.mark_non_differentiable(kl, rew)
+        return out[0], kl, rew
+
+    @staticmethod
+    def backward(ctx, g, _gk, _gr):
+        (dpol,) = ctx.saved_tensors
+        return dpol * g, None, None, None, None
+
+
+def reinforce_loss(policy_logp: torch.Tensor, ref_logp: torch.Tensor, scores: torch.Tensor, kl_coef: float,
+                   baseline: Optional[torch.Tensor] = None):
+    """``(loss, kl [B], rewards [B])`` of the reference's sequence-level REINFORCE (``R/src/training/train_rlhf.py:149-153``);
+    ``kl`` / ``rewards`` are detached statistics, the gradient flows through the loss only (as in the reference)."""
+    if not policy_logp.is_cuda:
+        loss, kl, rew = R.reinforce_loss(policy_logp, ref_logp, scores, kl_coef, baseline)
+        return loss, kl.detach(), rew.detach()
+    return _Reinforce.apply(policy_logp, ref_logp.detach(), scores.detach(), kl_coef, baseline)
+
+
+class _PPOLoss(Function):
+    @staticmethod
+    def forward(ctx, new_lp, old_lp, adv, values, old_values, returns, mask, clip, vclip, vf_coef):
+        n = new_lp.numel()
+        f = lambda t: _c(t.float()) if t is not None else None
+        new_c, old_c, adv_c, val_c, oval_c, ret_c, m_c = (f(t) for t in (new_lp, old_lp, adv, values, old_values, returns, mask))
+        out = torch.empty(5, dtype=torch.float32, device=new_lp.device)
+        dlp = torch.empty_like(new_c)
+        dv = torch.empty_like(val_c) if val_c is not None else None
+        q = lambda t: N.ptr(t) if t is not None else None
+        N.call("dla_ppo_loss", q(new_c), q(old_c), q(adv_c), q(val_c), q(oval_c), q(ret_c), q(m_c), n, float(clip), float(vclip),
+               float(vf_coef), N.ptr(out), N.ptr(dlp), q(dv), _s(new_c))
+        ctx.save_for_backward(dlp, dv if dv is not None else dlp)
+        ctx.has_v = dv is not None
+        ctx.shapes = (new_lp.shape, values.shape if values is not None else None)
+        stats = out[1:].clone()
+        ctx.mark_non_differentiable(stats)
+        return out[0], stats
+
+    @staticmethod
+    def backward(ctx, g, _gs):
+        dlp, dv = ctx.saved_tensors
+        return ((dlp * g).view(ctx.shapes[0]), None, None, (dv * g).view(ctx.shapes[1]) if ctx.has_v else None, None, None, None,
+                None, None, None)
+
+
+def ppo_loss(new_logp, old_logp, advantages, values, old_values, returns, mask, clip: float = 0.2, vclip: float = 0.2,
+             vf_coef: float = 0.5):
+    """Clipped PPO + clipped value loss, masked token mean.  Returns ``(loss, stats)`` with
+    ``stats = [pg_loss, vf_loss, approx_kl, clipfrac]`` (detached)."""
+    if not new_logp.is_cuda:
+        return R.ppo_loss(new_logp, old_logp, advantages, values, old_values, returns, mask, clip, vclip, vf_coef)
+    return _PPOLoss.apply(new_logp, old_logp.detach(), advantages.detach(), values, None if old_values is None else old_values.detach(),
+                          None if returns is None else returns.detach(), mask, clip, vclip, vf_coef)
+
+
+def gae(rewards: torch.Tensor, values: torch.Tensor, mask: torch.Tensor, gamma: float, lam: float, whiten: bool = False):
+    """``(advantages, returns)`` over ``[B, T]``; ``whiten`` normalises the advantages over the masked tokens."""
+    if not rewards.is_cuda:
+        return R.gae(rewards, values, mask, gamma, lam, whiten)
+    B, T = rewards.shape
+    r, v, m = (_c(t.float()) for t in (rewards, values, mask))
+    adv, ret = torch.empty_like(r), torch.empty_like(r)
+    N.call("dla_gae", N.ptr(r), N.ptr(v), N.ptr(m), N.ptr(adv), N.ptr(ret), B, T, float(gamma), float(lam), int(whiten), _s(r))
+    return adv, ret
+
+
+def distill_kl_rows(student_logits: torch.Tensor, teacher_logits, coef: Optional[torch.Tensor], temperature: float,
+                    want_kl: bool = True, want_grad: bool = False):
+    """Row-wise ensemble KL on fp32 logits ``[rows, V]`` (unit inner stride): ``(kl [rows] | None, dl bf16 [rows, V] | None)``
+    with ``dl = (softmax(s/T) - mean_k softmax(t_k/T)) * coef / T``.  CUDA only; see ``csrc/distill.cu``."""
+    import ctypes
+
+    rows, V = student_logits.shape
+    K = len(teacher_logits)
+    assert student_logits.dtype == torch.float32 and all(t.dtype == torch.float32 and t.shape == student_logits.shape for t in teacher_logits)
+    assert student_logits.stride(1) == 1 and all(t.stride(1) == 1 for t in teacher_logits)
+    ptrs = (ctypes.c_void_p * K)(*[t.data_ptr() for t in teacher_logits])
+    lds = (ctypes.c_int64 * K)(*[t.stride(0) for t in teacher_logits])
+    kl = torch.empty(rows, dtype=torch.float32, device=student_logits.device) if want_kl else None
+    dl = torch.empty(rows, V, dtype=BF16, device=student_logits.device) if want_grad else None
+    cf = _c(coef.float()) if coef is not None else None
+    N.call("dla_distill_kl", N.ptr(student_logits), student_logits.stride(0), ctypes.cast(ptrs, ctypes.c_void_p),
+           ctypes.cast(lds, ctypes.c_void_p), K, N.ptr(cf) if cf is not None else None, rows, V, float(temperature),
+           N.ptr(kl) if kl is not None else None, N.ptr(dl) if dl is not None else None, V, _s(student_logits))
+    return kl, dl

@@ -51,6 +51,12 @@ _SIGNATURES = {
     "dla_attn_decode": [P, P, P, P, P, I, I, I, I, I, F, P],
     "dla_gemm_skinny_bf16": [P, P, P, P, P, I, I, I, I64, I64, I64, I64, I, I, P],
     "dla_decode_attn_fused": [P, I64, P, P, P, P, P, P, I, I, I, I, I, I, F, P],
+    "dla_scalar_head_fwd": [P, P, P, P, P, P, I, I, I, I, P],
+    "dla_scalar_head_bwd": [P, P, P, P, P, P, P, P, I, I, I, I, P],
+    "dla_reinforce_loss": [P, P, P, I, F, P, P, P, P, P, P],
+    "dla_ppo_loss": [P, P, P, P, P, P, P, I, F, F, F, P, P, P, P],
+    "dla_gae": [P, P, P, P, P, I, I, F, F, I, P],
+    "dla_distill_kl": [P, I64, P, P, I, P, I, I, F, P, P, I64, P],
     "dla_sample_top_p": [P, I, I, I, I64, F, F, c_uint64, c_uint64, P, P, P],
     "dla_fused_rs_adamw": [P, P, I, I, I64, I64, F, P, P, P, P, P, F, F, F, F, F, F, F, P, I, P],
     "dla_peer_barrier": [P, I, I, I, c_uint32, I, P],

@@ -174,8 +174,9 @@ def top_p_sample(logits: torch.Tensor, temperature: float, top_p: float, generat
     return si.gather(-1, pick).squeeze(-1)
 
 
-def gae(rewards: torch.Tensor, values: torch.Tensor, mask: torch.Tensor, gamma: float, lam: float):
-    """Generalised advantage estimation over ``[B, T]`` token rewards/values (worklist #20)."""
+def gae(rewards: torch.Tensor, values: torch.Tensor, mask: torch.Tensor, gamma: float, lam: float, whiten: bool = False):
+    """Generalised advantage estimation over ``[B, T]`` token rewards/values (worklist #20); ``whiten`` normalises
+    the advantages over the masked tokens (returns keep the raw advantages)."""
     B, T = rewards.shape
     adv = torch.zeros_like(rewards)
     last = torch.zeros(B, dtype=rewards.dtype, device=rewards.device)
@@ -185,5 +186,52 @@ def gae(rewards: torch.Tensor, values: torch.Tensor, mask: torch.Tensor, gamma: 
         delta = rewards[:, t] + gamma * nxt * nm - values[:, t]
         last = delta + gamma * lam * nm * last
         adv[:, t] = last
-    adv = adv * mask.to(adv.dtype)
-    return adv, adv + values
+    m = mask.to(adv.dtype)
+    adv = adv * m
+    ret = adv + values
+    if whiten:
+        denom = m.sum().clamp(min=1)
+        mean = (adv * m).sum() / denom
+        std = (((adv - mean) ** 2 * m).sum() / denom).sqrt().clamp(min=1e-6)
+        adv = (adv - mean) / std * m
+    return adv, ret
+
+
+def ppo_loss(new_logp, old_logp, advantages, values, old_values, returns, mask, clip: float = 0.2, vclip: float = 0.2,
+             vf_coef: float = 0.5):
+    """Token-level clipped PPO objective + clipped value loss (masked mean); returns ``(loss, stats)`` with
+    ``stats = [pg_loss, vf_loss, approx_kl, clipfrac]``.  ``values`` may be None (policy term only)."""
+    m = mask.to(new_logp.dtype)
+    denom = m.sum().clamp(min=1)
+    ratio = torch.exp(new_logp - old_logp)
+    pg = torch.max(-advantages * ratio, -advantages * ratio.clamp(1 - clip, 1 + clip))
+    pg_loss = (pg * m).sum() / denom
+    if values is not None:
+        vclipped = old_values + (values - old_values).clamp(-vclip, vclip)
+        vf = 0.5 * torch.max((values - returns) ** 2, (vclipped - returns) ** 2)
+        vf_loss = (vf * m).sum() / denom
+    else:
+        vf_loss = torch.zeros((), dtype=new_logp.dtype, device=new_logp.device)
+    approx_kl = (0.5 * ((new_logp - old_logp) ** 2) * m).sum() / denom
+    clipfrac = (((ratio - 1).abs() > clip).to(m.dtype) * m).sum() / denom
+    stats = torch.stack([pg_loss.detach(), vf_loss.detach(), approx_kl.detach(), clipfrac.detach()])
+    return pg_loss + vf_coef * vf_loss, stats
+
+
+def scalar_head(hidden: torch.Tensor, mask: Optional[torch.Tensor], w: torch.Tensor, bias: Optional[torch.Tensor],
+                keep: Optional[torch.Tensor] = None, mode: str = "last_token") -> torch.Tensor:
+    """K10: pool (``last_token`` = index ``mask.sum(1) - 1``, ``mean`` = masked mean, ``token`` = none) -> dropout
+    mask -> ``Linear(H, 1)``; fp32 result ``[B]`` (``[B, T]`` for ``token``).  ``R/src/models/reward_model.py:54-64``."""
+    wv = w.float().reshape(-1)
+    b = bias.float().reshape(()) if bias is not None else 0.0
+    if mode == "token":
+        return hidden.float() @ wv + b
+    if mode == "last_token":
+        idx = (mask.sum(dim=1) - 1).clamp(min=0)
+        pooled = hidden[torch.arange(hidden.shape[0], device=hidden.device), idx].float()
+    else:
+        m = mask.unsqueeze(-1).float()
+        pooled = (hidden.float() * m).sum(1) / mask.sum(1, keepdim=True).clamp(min=1).float()
+    if keep is not None:
+        pooled = pooled * keep
+    return pooled @ wv + b

@@ -11,7 +11,7 @@ directly by its continuation, right-padded with ``pad_token_id``.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Callable, List, Optional
+from typing import List, Optional
 
 import torch
 
@@ -53,8 +53,13 @@ class _DecodeState:
 class _DecodeSession:
     cache: KVCache
     st: _DecodeState
-    pick: Callable[[], None]
-    advance: Callable[[], None]
+    rows: torch.Tensor
+    fused: bool
+    temp: float
+    top_p: float
+    eos: int
+    pad: int
+    max_len: int
     graph: Optional["torch.cuda.CUDAGraph"] = None
 
 
@@ -150,60 +155,78 @@ class Generator:
     # ---- decode session -----------------------------------------------------------------
     def _session(self, key: tuple, B: int, max_len: int, dev: torch.device, dtype: torch.dtype, temp: float, top_p: float,
                  eos: int, pad: int) -> "_DecodeSession":
-        """Fixed device buffers + the two halves of a decode step for one (batch, length, sampling) signature.
-        Sessions are kept (most recent two) so that repeated rollouts of the same shape — every PPO step —
-        replay the graph captured the first time instead of re-capturing it."""
+        """Fixed device buffers for one (batch, length, sampling) signature.  Sessions are kept (most recent two) so
+        that repeated rollouts of the same shape — every PPO step — replay the graph captured the first time.
+        A session holds no reference back to the generator: dropping the generator frees its graphs at once
+        (a CUDA graph must never be destroyed by the cyclic GC in the middle of another capture)."""
         ses = self._sessions.get(key)
         if ses is not None:
             return ses
         cfg = self.cfg
-        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
-        cache = KVCache(cfg, B, max_len, dev, dtype)
         st = _DecodeState(logits=torch.zeros(B, cfg.vocab_size, dtype=dtype, device=dev),
                           seqs=torch.full((B, max_len), pad, dtype=torch.long, device=dev),
                           lens=torch.zeros(B, dtype=torch.int32, device=dev), finished=torch.zeros(B, dtype=torch.bool, device=dev),
                           nxt=torch.zeros(B, dtype=torch.long, device=dev), counter=torch.zeros(1, dtype=torch.long, device=dev))
-        rows = torch.arange(B, device=dev)
-        fused = self._fused_decode_ok(dev, max_len)
-
-        def pick() -> None:
-            """Sample one token per row and update sequences / lengths / finished flags (no host sync)."""
-            nxt = sample(st.logits, temp, top_p, None, seed=_SEED_BASE, step=0, step_dev=st.counter)
-            nxt = torch.where(st.finished, torch.full_like(nxt, pad), nxt)
-            can = (~st.finished) & (st.lens < max_len)
-            idx = st.lens.long().clamp(max=max_len - 1)
-            st.seqs[rows, idx] = torch.where(can, nxt, st.seqs[rows, idx])
-            st.lens.add_(can.to(torch.int32))
-            st.finished.logical_or_((can & (nxt == eos)) | (st.lens >= max_len))
-            st.nxt.copy_(nxt)
-            st.counter.add_(1)
-
-        def advance() -> None:
-            """One decode forward for the tokens chosen by ``pick`` (position lens-1), refreshing ``st.logits``."""
-            tok_pos = (st.lens - 1).clamp(min=0)
-            x = F.embedding(st.nxt[:, None], self.p.acquire("embed")["tok_emb"], None)
-            if cfg.arch == "gpt2":
-                x = x + self.p.acquire("embed")["pos_emb"][tok_pos.long()][:, None]
-            self.p.release("embed")
-            pos64 = None if fused else tok_pos.long()
-            for i in range(cfg.num_layers):
-                w = self.p.acquire(f"layer.{i}")
-                if fused:
-                    attn = self._decode_layer_attention(w, x, cache, i, st.lens)
-                else:
-                    qkv = self._qkv(w, x, tok_pos[:, None])
-                    cache.k[i, rows, pos64] = qkv[:, 0, Hq:Hq + Hk]
-                    cache.v[i, rows, pos64] = qkv[:, 0, Hq + Hk:]
-                    attn = self._decode_attention(qkv[:, 0, :Hq].contiguous(), cache, i, st.lens)
-                x = self._post_attn(w, x, attn[:, None])
-                self.p.release(f"layer.{i}")
-            st.logits.copy_(self._final(x)[:, 0])
-
-        ses = _DecodeSession(cache=cache, st=st, pick=pick, advance=advance)
+        ses = _DecodeSession(cache=KVCache(cfg, B, max_len, dev, dtype), st=st, rows=torch.arange(B, device=dev),
+                             fused=self._fused_decode_ok(dev, max_len), temp=temp, top_p=top_p, eos=eos, pad=pad, max_len=max_len)
         while len(self._sessions) >= 2:
             self._sessions.pop(next(iter(self._sessions)))
         self._sessions[key] = ses
         return ses
+
+    def _pick(self, ses: "_DecodeSession") -> None:
+        """Sample one token per row and update sequences / lengths / finished flags (no host sync)."""
+        st, max_len = ses.st, ses.max_len
+        nxt = sample(st.logits, ses.temp, ses.top_p, None, seed=_SEED_BASE, step=0, step_dev=st.counter)
+        nxt = torch.where(st.finished, torch.full_like(nxt, ses.pad), nxt)
+        can = (~st.finished) & (st.lens < max_len)
+        idx = st.lens.long().clamp(max=max_len - 1)
+        st.seqs[ses.rows, idx] = torch.where(can, nxt, st.seqs[ses.rows, idx])
+        st.lens.add_(can.to(torch.int32))
+        st.finished.logical_or_((can & (nxt == ses.eos)) | (st.lens >= max_len))
+        st.nxt.copy_(nxt)
+        st.counter.add_(1)
+
+    def _advance(self, ses: "_DecodeSession") -> None:
+        """One decode forward for the tokens chosen by ``_pick`` (position lens-1), refreshing ``st.logits``."""
+        cfg, st, cache, rows = self.cfg, ses.st, ses.cache, ses.rows
+        Hq, Hk = cfg.num_heads, cfg.num_kv_heads
+        tok_pos = (st.lens - 1).clamp(min=0)
+        x = F.embedding(st.nxt[:, None], self.p.acquire("embed")["tok_emb"], None)
+        if cfg.arch == "gpt2":
+            x = x + self.p.acquire("embed")["pos_emb"][tok_pos.long()][:, None]
+        self.p.release("embed")
+        pos64 = None if ses.fused else tok_pos.long()
+        for i in range(cfg.num_layers):
+            w = self.p.acquire(f"layer.{i}")
+            if ses.fused:
+                attn = self._decode_layer_attention(w, x, cache, i, st.lens)
+            else:
+                qkv = self._qkv(w, x, tok_pos[:, None])
+                cache.k[i, rows, pos64] = qkv[:, 0, Hq:Hq + Hk]
+                cache.v[i, rows, pos64] = qkv[:, 0, Hq + Hk:]
+                attn = self._decode_attention(qkv[:, 0, :Hq].contiguous(), cache, i, st.lens)
+            x = self._post_attn(w, x, attn[:, None])
+            self.p.release(f"layer.{i}")
+        st.logits.copy_(self._final(x)[:, 0])
+
+    def _capture(self, ses: "_DecodeSession") -> None:
+        """Record ``_advance`` + ``_pick`` as one CUDA graph.  Garbage collection is run first and held off during
+        the capture: freeing an unrelated dead CUDA graph while a stream is capturing invalidates the capture."""
+        import gc
+
+        gc.collect()
+        was_enabled = gc.isenabled()
+        gc.disable()
+        try:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self._advance(ses)
+                self._pick(ses)
+            ses.graph = graph
+        finally:
+            if was_enabled:
+                gc.enable()
 
     def reset(self) -> None:
         """Drop cached decode sessions (KV buffers and captured graphs), e.g. after parameters were re-allocated."""
@@ -248,26 +271,23 @@ class Generator:
         done = 0
         with F.weights_static():      # nothing in this stream writes the weights until generation returns
             if steps > 0:
-                ses.pick()
+                self._pick(ses)
                 done = 1
             if ses.graph is None and self._graphable(dev) and steps > 4:
                 # one eager token first (work areas and device binding exist before capture), then capture
-                # "forward + pick" once: ~12 launches per layer collapse into one graph launch per token
-                ses.advance()
-                ses.pick()
+                # "forward + pick" once: ~12 launches per layer collapse into one graph launch per token.
+                # Capture only records; the state is untouched until the first replay.
+                self._advance(ses)
+                self._pick(ses)
                 done = 2
-                ses.graph = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(ses.graph):
-                    ses.advance()
-                    ses.pick()
-                # capture only records; the state is untouched until the first replay
+                self._capture(ses)
             use_graph = ses.graph is not None and self.use_cuda_graph
             while done < steps:
                 if use_graph:
                     ses.graph.replay()
                 else:
-                    ses.advance()
-                    ses.pick()
+                    self._advance(ses)
+                    self._pick(ses)
                 done += 1
                 if done % self.finish_check_every == 0 and done < steps and bool(st.finished.all()):
                     break

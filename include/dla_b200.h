@@ -204,6 +204,38 @@ int dla_decode_attn_fused(void* qkv, int64_t qkv_stride, void* kcache, void* vca
                           const float* cos_t, const float* sin_t, int B, int S_max, int Hq, int Hk, int D,
                           int rot_dim, float scale, void* stream);
 
+/* ---------------------------------------------------------------- scalar heads, RL objectives, distillation */
+/* Reward / value head (csrc/heads.cu).  hidden bf16 [B,T,H], mask int64 [B,T], w bf16 [H], bias bf16 [1] (nullable),
+ * keep fp32 [B,H] dropout mask already scaled by 1/(1-p) (nullable).  mode 0: out[b] = w.(keep*hidden[b, n_b-1]);
+ * mode 1: masked mean pooling; mode 2: out[b,t] per token (mask/keep unused).  bwd writes dense dhidden (nullable)
+ * and ACCUMULATES fp32 dw[H], db[1] (nullable; caller zeroes).  R: R/src/models/reward_model.py:44,54-64. */
+int dla_scalar_head_fwd(const void* hidden, const int64_t* mask, const void* w, const void* bias, const float* keep,
+                        float* out, int B, int T, int H, int mode, void* stream);
+int dla_scalar_head_bwd(const void* hidden, const int64_t* mask, const void* w, const float* keep, const float* dout,
+                        void* dhidden, float* dw, float* db, int B, int T, int H, int mode, void* stream);
+
+/* Sequence-level REINFORCE: out = {loss, mean kl, mean reward}; kl_out/rew_out [B] and dpol [B] nullable; baseline
+ * (device scalar, nullable) overrides the batch-mean baseline.  R: R/src/training/train_rlhf.py:149-153. */
+int dla_reinforce_loss(const float* pol, const float* ref, const float* score, int B, float kl_coef,
+                       const float* baseline, float* out, float* kl_out, float* rew_out, float* dpol, void* stream);
+/* Token-level clipped PPO + clipped value loss over N masked elements: out = {loss, pg, vf, approx_kl, clipfrac};
+ * values/old_values/returns nullable together.  GAE (+ optional advantage whitening) over [B,T].  Beyond the
+ * reference: the `ppo.*` keys of R/config/rlhf_config.yaml:14,17 (SURVEY worklist #20). */
+int dla_ppo_loss(const float* new_logp, const float* old_logp, const float* adv, const float* values,
+                 const float* old_values, const float* returns, const float* mask, int N, float clip, float vclip,
+                 float vf_coef, float* out, float* dlogp, float* dvalues, void* stream);
+int dla_gae(const float* rewards, const float* values, const float* mask, float* adv, float* ret, int B, int T,
+            float gamma, float lam, int whiten, void* stream);
+
+/* Distillation KL per logits row (csrc/distill.cu): kl_out[r] = KL(mean_k softmax(t_k/T) || softmax(s/T)) and/or
+ * dl[r,:] = (softmax(s/T) - mean_k softmax(t_k/T)) * coef[r] / T in bf16.  student / teachers fp32 [rows, V] with
+ * pitches in elements; teacher_ptrs / teacher_ld are HOST arrays of n_teachers (<= dla_distill_max_teachers())
+ * device pointers / pitches.  R: R/src/training/train_distill.py:132-144. */
+int dla_distill_kl(const float* student, int64_t ld_s, const float* const* teacher_ptrs, const int64_t* teacher_ld,
+                   int n_teachers, const float* coef, int rows, int V, float temperature, float* kl_out, void* dl,
+                   int64_t ld_d, void* stream);
+int dla_distill_max_teachers(void);
+
 /* ---------------------------------------------------------------- sampling (K16) */
 /* Per-row temperature + top-p + multinomial on fp32/bf16 logits [B,V]; writes int64 token ids.
  * seed/offset: counter RNG; offset_dev (nullable) is a device int64 added to offset inside the kernel, so a

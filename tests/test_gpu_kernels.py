@@ -420,3 +420,92 @@ def test_gemm_skinny_decode_shapes(native_lib, M, N, K):
     # the tensor-core tile kernel must agree on the same operands (33 rows take the tcgen05 path)
     a33 = torch.cat([a, a[:1].expand(33 - M, K)], 0).contiguous()
     _close(F.gemm(a33, b)[:M], ref, rtol=2e-2, atol=0.02 * math.sqrt(K), what="tile kernel on the same operands")
+
+
+@pytest.mark.parametrize("mode", ["last_token", "mean", "token"])
+def test_scalar_head_fwd_bwd(native_lib, mode):
+    """Reward / value head kernel (csrc/heads.cu) against the fp32 PyTorch restatement, gradients included."""
+    torch.manual_seed(21)
+    B, T, H = 5, 70, 512
+    hid = _rand(B, T, H).requires_grad_()
+    w = (_rand(1, H) * 0.1).requires_grad_()
+    b = _rand(1).requires_grad_()
+    mask = torch.zeros(B, T, dtype=torch.long, device=DEV)
+    for i, n in enumerate([70, 1, 33, 64, 17]):
+        mask[i, :n] = 1
+    keep = None if mode == "token" else (torch.rand(B, H, device=DEV) > 0.1).float() / 0.9
+    out = F.scalar_head(hid, mask, w, b, keep, mode)
+    h2, w2, b2 = (t.detach().float().requires_grad_() for t in (hid, w, b))
+    ref = R.scalar_head(h2, mask, w2, b2, keep, mode)
+    _close(out, ref, atol=3e-2, what=f"scalar head {mode}")
+    g = torch.randn_like(ref)
+    out.backward(g)
+    ref.backward(g)
+    _close(hid.grad, h2.grad, atol=2e-2, what="dhidden")
+    _close(w.grad, w2.grad, rtol=3e-2, atol=0.3, what="dw")
+    _close(b.grad, b2.grad, rtol=2e-2, atol=5e-2, what="db")
+
+
+def test_rl_objective_kernels(native_lib):
+    """csrc/rl.cu: REINFORCE, clipped PPO (+value loss) and GAE with whitening against the PyTorch formulas."""
+    torch.manual_seed(23)
+    B, T = 6, 50
+    pol = torch.randn(B, device=DEV).requires_grad_()
+    ref, sc = torch.randn(B, device=DEV), torch.randn(B, device=DEV)
+    for base in (None, torch.tensor(0.3, device=DEV)):
+        loss, kl, rew = F.reinforce_loss(pol, ref, sc, 0.1, base)
+        p2 = pol.detach().clone().requires_grad_()
+        l2, kl2, rew2 = R.reinforce_loss(p2, ref, sc, 0.1, base)
+        _close(loss, l2, atol=1e-5, what="reinforce loss")
+        _close(kl, kl2, atol=1e-6, what="kl")
+        _close(rew, rew2, atol=1e-6, what="rewards")
+        (g1,) = torch.autograd.grad(loss, pol)
+        (g2,) = torch.autograd.grad(l2, p2)
+        _close(g1, g2, atol=1e-6, what="reinforce grad")
+
+    mask = (torch.rand(B, T, device=DEV) > 0.3).float()
+    old_lp = -torch.rand(B, T, device=DEV) * 3
+    new_lp = (old_lp + 0.4 * torch.randn(B, T, device=DEV)).requires_grad_()
+    adv = torch.randn(B, T, device=DEV)
+    old_v = torch.randn(B, T, device=DEV)
+    val = (old_v + 0.5 * torch.randn(B, T, device=DEV)).requires_grad_()
+    ret = torch.randn(B, T, device=DEV)
+    loss, st = F.ppo_loss(new_lp, old_lp, adv, val, old_v, ret, mask, 0.2, 0.3, 0.5)
+    n2, v2 = new_lp.detach().clone().requires_grad_(), val.detach().clone().requires_grad_()
+    l2, st2 = R.ppo_loss(n2, old_lp, adv, v2, old_v, ret, mask, 0.2, 0.3, 0.5)
+    _close(loss, l2, atol=1e-5, what="ppo loss")
+    _close(st, st2, atol=1e-5, what="ppo stats")
+    loss.backward()
+    l2.backward()
+    _close(new_lp.grad, n2.grad, atol=1e-6, what="dlogp")
+    _close(val.grad, v2.grad, atol=1e-6, what="dvalues")
+    lp_only, _ = F.ppo_loss(new_lp, old_lp, adv, None, None, None, mask, 0.2, 0.3, 0.5)
+    _close(lp_only, R.ppo_loss(n2, old_lp, adv, None, None, None, mask, 0.2, 0.3, 0.5)[0], atol=1e-5, what="ppo policy term only")
+
+    rewards = torch.randn(B, T, device=DEV)
+    m = torch.zeros(B, T, device=DEV)
+    for i, n in enumerate([50, 3, 20, 1, 49, 11]):
+        m[i, 5:5 + min(n, T - 5)] = 1
+    for whiten in (False, True):
+        a1, r1 = F.gae(rewards, old_v * m, m, 0.99, 0.95, whiten)
+        a2, r2 = R.gae(rewards, old_v * m, m, 0.99, 0.95, whiten)
+        _close(a1, a2, atol=1e-4, what=f"gae advantages (whiten={whiten})")
+        _close(r1, r2, atol=1e-4, what="gae returns")
+
+
+@pytest.mark.parametrize("K,V,temp", [(1, 1000, 1.0), (3, 4099, 2.0), (2, 128256, 1.0)])
+def test_distill_kl_rows(native_lib, K, V, temp):
+    """csrc/distill.cu against kl_div(log_softmax(student), mean softmax(teachers)) and its autograd gradient."""
+    torch.manual_seed(29)
+    rows = 9
+    s = (torch.randn(rows, V, device=DEV) * 3).requires_grad_()
+    ts = [torch.randn(rows, V, device=DEV) * 3 for _ in range(K)]
+    coef = torch.rand(rows, device=DEV)
+    kl, dl = F.distill_kl_rows(s.detach(), ts, coef, temp, want_kl=True, want_grad=True)
+    slp = torch.log_softmax(s / temp, -1)
+    tp = torch.stack([torch.softmax(t / temp, -1) for t in ts]).mean(0)
+    ref = torch.nn.functional.kl_div(slp, tp, reduction="none").sum(-1)
+    _close(kl, ref, rtol=1e-3, atol=1e-4, what="kl rows")
+    (ref * coef).sum().backward()
+    err = (dl.float() - s.grad).norm() / s.grad.norm()
+    assert err < 1e-2, f"distill grad relative error {err:.3g}"
