@@ -45,6 +45,8 @@ def parse() -> argparse.Namespace:
     ap.add_argument("--sharding", default=os.environ.get("DLA_BENCH_SHARDING", "zero3"))
     ap.add_argument("--comm", default=os.environ.get("DLA_BENCH_COMM", "auto"))
     ap.add_argument("--state-dtype", default=os.environ.get("DLA_BENCH_STATE", "fp32"))
+    ap.add_argument("--resident", default=os.environ.get("DLA_BENCH_RESIDENT", "auto"), choices=["auto", "0", "1"],
+                    help="keep gathered parameters resident (auto = by HBM size; 0 = stream units, the 70B mode)")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
 
@@ -135,7 +137,8 @@ def main() -> None:
         from dla_b200.ops import native
         from dla_b200.optim import AdamWConfig
 
-        plan = HardwarePlan(sharding=args.sharding if world > 1 else "ddp", comm=args.comm, optimizer_state_dtype=args.state_dtype)
+        plan = HardwarePlan(sharding=args.sharding if world > 1 else "ddp", comm=args.comm, optimizer_state_dtype=args.state_dtype,
+                            resident_params=None if args.resident == "auto" else args.resident == "1")
         policy = load_causal_lm(args.model, ctx, plan, gradient_checkpointing=True, seed=0, name="policy")
         ref = load_causal_lm(args.model, ctx, plan, gradient_checkpointing=False, trainable=False, seed=0, name="reference")
         opt = AdamWConfig(lr=1e-6, weight_decay=0.01, max_grad_norm=1.0)

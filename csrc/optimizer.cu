@@ -7,14 +7,59 @@ namespace dla {
 constexpr int kSumsqBlocks = kNumSMs * 8;
 constexpr int kSumsqThreads = 256;
 
-// One thread = 8 consecutive elements: 16 B of grad, 3 x 32 B of fp32 state in, 3 x 32 B + 16 B out.
-template <bool kGradF32>
+// bf16 Adam moments (70B sizing: 4 instead of 8 bytes of moments per parameter).  Round-to-nearest would freeze
+// v once (1-beta2) g^2 drops under half a bf16 ulp of v, so the store rounds stochastically: the low 16 bits of
+// the fp32 value plus a 16-bit hash of (element, step) carry into the kept half.
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16;
+  x *= 0x7feb352du;
+  x ^= x >> 15;
+  x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
+__device__ __forceinline__ bf16 to_bf16_stochastic(float x, uint32_t rnd16) {
+  const uint32_t bits = __float_as_uint(x) + (rnd16 & 0xFFFFu);
+  __nv_bfloat16_raw r;
+  r.x = (unsigned short)(bits >> 16);
+  return bf16(r);
+}
+template <bool kBF16>
+__device__ __forceinline__ void load_moment8(const void* base, int64_t o, float* out) {
+  if (kBF16) {
+    unpack8(ld8(reinterpret_cast<const bf16*>(base) + o), out);
+  } else {
+    const float* f = reinterpret_cast<const float*>(base) + o;
+    *reinterpret_cast<float4*>(out) = *reinterpret_cast<const float4*>(f);
+    *reinterpret_cast<float4*>(out + 4) = *reinterpret_cast<const float4*>(f + 4);
+  }
+}
+template <bool kBF16>
+__device__ __forceinline__ void store_moment8(void* base, int64_t o, const float* in, uint32_t seed) {
+  if (kBF16) {
+    bf16x8 pk;
+    bf16* e = reinterpret_cast<bf16*>(&pk);
+    const uint32_t h = mix32(seed ^ (uint32_t)o ^ (uint32_t)(o >> 32) * 0x9E3779B9u);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) e[j] = to_bf16_stochastic(in[j], mix32(h + j));
+    st8(reinterpret_cast<bf16*>(base) + o, pk);
+  } else {
+    float* f = reinterpret_cast<float*>(base) + o;
+    *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(in);
+    *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(in + 4);
+  }
+}
+
+// One thread = 8 consecutive elements: 16 B of grad, 3 x 32 B of fp32 state in, 3 x 32 B + 16 B out
+// (2 x 16 B each way for the moments when they are bf16).
+template <bool kGradF32, bool kMomBF16>
 __global__ void __launch_bounds__(256)
-adamw_kernel(float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
+adamw_kernel(float* __restrict__ master, void* __restrict__ m, void* __restrict__ v,
              const void* __restrict__ grad, bf16* __restrict__ param, int64_t n, float lr, float beta1,
              float beta2, float eps, float wd, float inv_bc1, float inv_sqrt_bc2,
              const float* __restrict__ grad_scale_dev, float prescale) {
   const float gs = prescale * (grad_scale_dev != nullptr ? *grad_scale_dev : 1.f);
+  const uint32_t step_seed = __float_as_uint(inv_sqrt_bc2) * 0x9E3779B9u;   // changes every optimizer step
   const int64_t nvec = n >> 3;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t o = i * 8;
@@ -27,10 +72,8 @@ adamw_kernel(float* __restrict__ master, float* __restrict__ m, float* __restric
     }
     *reinterpret_cast<float4*>(p) = *reinterpret_cast<const float4*>(master + o);
     *reinterpret_cast<float4*>(p + 4) = *reinterpret_cast<const float4*>(master + o + 4);
-    *reinterpret_cast<float4*>(mm) = *reinterpret_cast<const float4*>(m + o);
-    *reinterpret_cast<float4*>(mm + 4) = *reinterpret_cast<const float4*>(m + o + 4);
-    *reinterpret_cast<float4*>(vv) = *reinterpret_cast<const float4*>(v + o);
-    *reinterpret_cast<float4*>(vv + 4) = *reinterpret_cast<const float4*>(v + o + 4);
+    load_moment8<kMomBF16>(m, o, mm);
+    load_moment8<kMomBF16>(v, o, vv);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float gj = g[j] * gs;
@@ -41,21 +84,26 @@ adamw_kernel(float* __restrict__ master, float* __restrict__ m, float* __restric
     }
     *reinterpret_cast<float4*>(master + o) = *reinterpret_cast<float4*>(p);
     *reinterpret_cast<float4*>(master + o + 4) = *reinterpret_cast<float4*>(p + 4);
-    *reinterpret_cast<float4*>(m + o) = *reinterpret_cast<float4*>(mm);
-    *reinterpret_cast<float4*>(m + o + 4) = *reinterpret_cast<float4*>(mm + 4);
-    *reinterpret_cast<float4*>(v + o) = *reinterpret_cast<float4*>(vv);
-    *reinterpret_cast<float4*>(v + o + 4) = *reinterpret_cast<float4*>(vv + 4);
+    store_moment8<kMomBF16>(m, o, mm, step_seed);
+    store_moment8<kMomBF16>(v, o, vv, step_seed ^ 0xA5A5A5A5u);
     if (param != nullptr) st8(param + o, pack8(p));
   }
   // tail (n % 8) handled by the first threads of block 0
   if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
     const int64_t o = (nvec << 3) + threadIdx.x;
     float gj = (kGradF32 ? ((const float*)grad)[o] : __bfloat162float(((const bf16*)grad)[o])) * gs;
-    float mj = beta1 * m[o] + (1.f - beta1) * gj;
-    float vj = beta2 * v[o] + (1.f - beta2) * gj * gj;
+    const float m0 = kMomBF16 ? __bfloat162float(((const bf16*)m)[o]) : ((const float*)m)[o];
+    const float v0 = kMomBF16 ? __bfloat162float(((const bf16*)v)[o]) : ((const float*)v)[o];
+    float mj = beta1 * m0 + (1.f - beta1) * gj;
+    float vj = beta2 * v0 + (1.f - beta2) * gj * gj;
     float pj = master[o] * (1.f - lr * wd) - lr * inv_bc1 * (mj / (sqrtf(vj) * inv_sqrt_bc2 + eps));
-    m[o] = mj;
-    v[o] = vj;
+    if (kMomBF16) {
+      ((bf16*)m)[o] = to_bf16_stochastic(mj, mix32(step_seed + (uint32_t)o));
+      ((bf16*)v)[o] = to_bf16_stochastic(vj, mix32(step_seed + (uint32_t)o + 0x51ED27u));
+    } else {
+      ((float*)m)[o] = mj;
+      ((float*)v)[o] = vj;
+    }
     master[o] = pj;
     if (param != nullptr) param[o] = __float2bfloat16(pj);
   }
@@ -132,9 +180,9 @@ extern "C" {
 
 int dla_sumsq_blocks(void) { return kSumsqBlocks; }
 
-int dla_adamw(float* master, float* m, float* v, const void* grad, void* param, int64_t n, float lr, float beta1,
+int dla_adamw(float* master, void* m, void* v, const void* grad, void* param, int64_t n, float lr, float beta1,
               float beta2, float eps, float weight_decay, float bias_c1, float bias_c2,
-              const float* grad_scale_dev, float grad_prescale, int grad_is_fp32, void* stream) {
+              const float* grad_scale_dev, float grad_prescale, int flags, void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
   DLA_REQUIRE(bias_c1 > 0.f && bias_c2 > 0.f, DLA_E_BADARG, "adamw: bias corrections must be > 0");
   if (n == 0) return 0;
@@ -142,12 +190,16 @@ int dla_adamw(float* master, float* m, float* v, const void* grad, void* param, 
   if (blocks < 1) blocks = 1;
   if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
   const float inv_bc1 = 1.f / bias_c1, inv_sqrt_bc2 = 1.f / sqrtf(bias_c2);
-  if (grad_is_fp32)
-    adamw_kernel<true><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(master, m, v, grad, (bf16*)param, n, lr, beta1, beta2, eps,
-                                                                     weight_decay, inv_bc1, inv_sqrt_bc2, grad_scale_dev, grad_prescale);
-  else
-    adamw_kernel<false><<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(master, m, v, grad, (bf16*)param, n, lr, beta1, beta2, eps,
-                                                                      weight_decay, inv_bc1, inv_sqrt_bc2, grad_scale_dev, grad_prescale);
+  const bool g32 = (flags & DLA_ADAMW_GRAD_FP32) != 0, mom16 = (flags & DLA_ADAMW_MOMENTS_BF16) != 0;
+  cudaStream_t st = (cudaStream_t)stream;
+#define DLA_ADAMW_LAUNCH(G, M)                                                                                              \
+  adamw_kernel<G, M><<<(int)blocks, 256, 0, st>>>(master, m, v, grad, (bf16*)param, n, lr, beta1, beta2, eps, weight_decay, \
+                                                  inv_bc1, inv_sqrt_bc2, grad_scale_dev, grad_prescale)
+  if (g32 && mom16) DLA_ADAMW_LAUNCH(true, true);
+  else if (g32) DLA_ADAMW_LAUNCH(true, false);
+  else if (mom16) DLA_ADAMW_LAUNCH(false, true);
+  else DLA_ADAMW_LAUNCH(false, false);
+#undef DLA_ADAMW_LAUNCH
   return check_launch("adamw");
 }
 

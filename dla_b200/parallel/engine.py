@@ -59,6 +59,9 @@ class Engine(ParamProvider):
         self.dtype = dtype or (torch.bfloat16 if self.device.type == "cuda" else torch.float32)
         self.grad_dtype = grad_dtype or self.dtype
         self.state_dtype = state_dtype
+        if state_dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError(f"optimizer_state_dtype must be fp32 or bf16, got {state_dtype}")
+        self._moment_flag = 2 if state_dtype == torch.bfloat16 else 0      # DLA_ADAMW_MOMENTS_BF16
         self.W = ctx.world_size if self.sharding in SHARDED else 1     # shard group size
         self.r = ctx.rank if self.W > 1 else 0
         self.comm = comm
@@ -446,7 +449,7 @@ class Engine(ParamProvider):
             if cuda:
                 N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]), N.ptr(g),
                        N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef),
-                       prescale, int(g.dtype == torch.float32), N.stream_ptr(self.device))
+                       prescale, int(g.dtype == torch.float32) | self._moment_flag, N.stream_ptr(self.device))
             else:
                 R.adamw_step(self.master[u.name], self.m[u.name], self.v[u.name], g, lr, b1, b2, opt.eps,
                              opt.weight_decay, t, grad_scale=prescale * coef)
@@ -471,20 +474,20 @@ class Engine(ParamProvider):
         fc, s = self.fc, N.stream_ptr(self.device)
         b1, b2 = opt.betas
         clip_on = bool(opt.max_grad_norm and opt.max_grad_norm > 0)
-        if clip_on:
+        if clip_on or self._moment_flag:        # the single-kernel reduce+AdamW keeps fp32 moments only
             self._sumsq.zero_()
             for u in self.units:
                 off = self.base[u.name] + self.r * self.S[u.name]
                 fc.reduce_shard(self.grad_arena, off, self.S[u.name], prescale, self.gred[u.name], self._sumsq)
                 self.stats["reduce_bytes"] += self.S[u.name] * _bytes(self.grad_dtype) * (self.W - 1)
             dist.all_reduce(self._sumsq, group=self.ctx.group)
-            N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm), N.ptr(self._coef), N.ptr(self._norm), s)
+            N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
             self.last_grad_norm = self._norm
             for u in self.units:
                 sh, off = self.shard[u.name], self.base[u.name] + self.r * self.S[u.name]
                 N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]),
                        N.ptr(self.gred[u.name]), N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2,
-                       N.ptr(self._coef), 1.0, 1, s)
+                       N.ptr(self._coef), 1.0, 1 | self._moment_flag, s)
                 fc.push_shard(sh, self.param_arena, off)
                 self.stats["allgather_bytes"] += sh.numel() * _bytes(self.dtype) * (self.W - 1)
         else:

@@ -87,11 +87,15 @@ int dla_embedding_bwd(const int64_t* ids, const void* dout, void* dtable, void* 
 /* Fused AdamW on a flat shard: reads bf16 grad, updates fp32 master/m/v, writes the bf16 param.
  * grad_scale_dev (nullable): device fp32 scalar multiplied into the gradient (clip factor), so no
  * host sync sits between the norm and the update.  R: torch.optim.AdamW at
- * R/src/training/train_dpo.py:73-77,120. */
-int dla_adamw(float* master, float* m, float* v, const void* grad, void* param, int64_t n,
+ * R/src/training/train_dpo.py:73-77,120.
+ * flags: DLA_ADAMW_GRAD_FP32 = grad is fp32 (else bf16); DLA_ADAMW_MOMENTS_BF16 = m and v are bf16 buffers, stored
+ * with stochastic rounding (halves the moment memory: the 70B-on-8-GPU sizing). */
+#define DLA_ADAMW_GRAD_FP32     1
+#define DLA_ADAMW_MOMENTS_BF16  2
+int dla_adamw(float* master, void* m, void* v, const void* grad, void* param, int64_t n,
               float lr, float beta1, float beta2, float eps, float weight_decay,
               float bias_c1, float bias_c2, const float* grad_scale_dev, float grad_prescale,
-              int grad_is_fp32, void* stream);
+              int flags, void* stream);
 /* out[0] (+)= sum(x^2). scratch: fp32 [dla_sumsq_blocks()].  R: clip_grad_norm_ at
  * R/src/training/utils.py:121-123. */
 int dla_sumsq(const void* x, int64_t n, int is_fp32, float* scratch, float* out, int accumulate,

@@ -223,6 +223,31 @@ def test_adamw_and_norm(native_lib):
     _close(param, ref_p.detach(), rtol=1e-2, atol=1e-2, what="adamw bf16 param")
 
 
+def test_adamw_bf16_moments_track_fp32(native_lib):
+    """bf16 (stochastically rounded) Adam moments: 50 steps on a slowly varying gradient must stay close to the
+    fp32-moment update — with round-to-nearest, v would stall at beta2 = 0.999."""
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(31)
+    n = 64 * 1024 + 5
+    base = torch.randn(n, device=DEV)
+    masters = [torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)]
+    moms = [(torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)),
+            (torch.zeros(n, device=DEV, dtype=BF16), torch.zeros(n, device=DEV, dtype=BF16))]
+    param = torch.empty(n, device=DEV, dtype=BF16)
+    for step in range(1, 51):
+        grad = (base * (1 + 0.1 * math.sin(step)) + 0.05 * torch.randn(n, device=DEV)).to(BF16)
+        for (mm, vv), master, flag in zip(moms, masters, (0, 2)):
+            N.call("dla_adamw", N.ptr(master), N.ptr(mm), N.ptr(vv), N.ptr(grad), N.ptr(param), n, 1e-3, 0.9, 0.999, 1e-8, 0.0,
+                   1 - 0.9 ** step, 1 - 0.999 ** step, None, 1.0, flag, N.stream_ptr())
+    v32, v16 = moms[0][1], moms[1][1].float()
+    rel_v = ((v16 - v32).abs().sum() / v32.abs().sum()).item()
+    assert rel_v < 2e-2, f"bf16 second moment drifted {rel_v:.3g} from fp32"
+    assert abs(v16.sum().item() / v32.sum().item() - 1) < 1e-3, "stochastic rounding must be unbiased"
+    rel_p = ((masters[1] - masters[0]).norm() / masters[0].norm()).item()
+    assert rel_p < 2e-2, f"parameters diverged {rel_p:.3g}"
+
+
 def test_losses(native_lib):
     torch.manual_seed(10)
     B = 37
