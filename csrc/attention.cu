@@ -15,33 +15,12 @@
 // HF generate's per-token SDPA (R/src/training/train_rlhf.py:124).
 #include <math.h>
 
-#include "tc_common.cuh"
+#include "attn_common.cuh"
 
 namespace dla {
 namespace attn {
 
-constexpr int BQ = 128;
-constexpr int BKV = 128;
 constexpr int kFwdThreads = 320;     // TMA warp, MMA warp, 2 x 4 softmax / row-owner warps (forward and backward)
-constexpr float kLog2e = 1.4426950408889634f;
-constexpr float kLn2 = 0.6931471805599453f;
-
-struct Params {
-  int B, T, Hq, Hk, D;
-  float scale;
-  int causal;
-  const int32_t* seqlens;
-  // forward
-  bf16* o;
-  int64_t o_sb, o_st, o_sh;
-  float* lse;        // [B, Hq, T]
-  // backward
-  const float* delta;  // [B, Hq, T]
-  float* dq_acc;       // [B, T, Hq, D] fp32
-  bf16* dk;
-  bf16* dv;
-  int64_t dkv_sb, dkv_st, dkv_sh;
-};
 
 // byte offset of element (row, col) in a [128 rows x 128 cols] bf16 tile stored as two 128B-swizzled
 // K-major blocks of 64 columns (the layout TMA SWIZZLE_128B produces and UMMA consumes)
@@ -49,17 +28,6 @@ __device__ __forceinline__ uint32_t sw128_offset(int row, int col) {
   const int blk = col >> 6;
   const int chunk = (col & 63) >> 3;
   return (uint32_t)(blk * 16384 + row * 128 + ((chunk ^ (row & 7)) << 4) + ((col & 7) << 1));
-}
-
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
-  bf162 v = __floats2bfloat162_rn(a, b);
-  return *reinterpret_cast<uint32_t*>(&v);
 }
 
 // ============================================================================== forward
@@ -678,20 +646,20 @@ attn_decode_kernel(const bf16* __restrict__ q, const bf16* __restrict__ kc, cons
   }
 }
 
-static int make_qkv_map(CUtensorMap* m, const void* base, int B, int T, int H, int D, int64_t sb, int64_t st, int64_t sh) {
-  const uint64_t dims[4] = {(uint64_t)D, (uint64_t)H, (uint64_t)T, (uint64_t)B};
-  const uint64_t strides[3] = {(uint64_t)sh, (uint64_t)st, (uint64_t)sb};
-  const uint32_t box[4] = {64, 1, 128, 1};
-  return make_tmap_4d_bf16(m, base, dims, strides, box);
-}
-
 }  // namespace attn
 }  // namespace dla
 
 using namespace dla;
 using namespace dla::attn;
 
+static int g_fwd_variant = 0;     // 0 = auto (ping-pong kernel), 1 = first-generation kernel, 2 = ping-pong kernel
+
 extern "C" {
+
+int dla_attn_set_fwd_variant(int v) {
+  g_fwd_variant = v;
+  return 0;
+}
 
 int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int T, int Hq, int Hk, int D,
                  int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh, int64_t o_sb,
@@ -710,6 +678,7 @@ int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
   p.o = (bf16*)o; p.o_sb = o_sb; p.o_st = o_st; p.o_sh = o_sh; p.lse = lse;
   dim3 grid((T + BQ - 1) / BQ, Hq, B);
   cudaStream_t s = (cudaStream_t)stream;
+  if (g_fwd_variant != 1) return attn_fwd2_dispatch(tmQ, tmK, tmV, p, s);     // ping-pong kernel (attn_fwd2.cu)
   if (D == 128) {
     constexpr int smem = 128 * 128 * 2 + 2 * 2 * 128 * 128 * 2 + 128 * 128 * 2 + 1024 + 4096;
     static bool set = false;

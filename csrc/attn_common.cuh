@@ -1,0 +1,54 @@
+// Shared pieces of the attention kernels (attention.cu: backward, decode, first-generation forward;
+// attn_fwd2.cu: ping-pong forward).
+#pragma once
+#include "tc_common.cuh"
+
+namespace dla {
+namespace attn {
+
+constexpr int BQ = 128;
+constexpr int BKV = 128;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+struct Params {
+  int B, T, Hq, Hk, D;
+  float scale;
+  int causal;
+  const int32_t* seqlens;
+  // forward
+  bf16* o;
+  int64_t o_sb, o_st, o_sh;
+  float* lse;        // [B, Hq, T]
+  // backward
+  const float* delta;  // [B, Hq, T]
+  float* dq_acc;       // [B, T, Hq, D] fp32
+  bf16* dk;
+  bf16* dv;
+  int64_t dkv_sb, dkv_st, dkv_sh;
+};
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
+  bf162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// 4-D map over a [B, T, H, D] view with arbitrary element strides; box = 64 (d) x 1 (head) x 128 (tokens) x 1 (batch)
+inline int make_qkv_map(CUtensorMap* m, const void* base, int B, int T, int H, int D, int64_t sb, int64_t st, int64_t sh) {
+  const uint64_t dims[4] = {(uint64_t)D, (uint64_t)H, (uint64_t)T, (uint64_t)B};
+  const uint64_t strides[3] = {(uint64_t)sh, (uint64_t)st, (uint64_t)sb};
+  const uint32_t box[4] = {64, 1, 128, 1};
+  return make_tmap_4d_bf16(m, base, dims, strides, box);
+}
+
+// attn_fwd2.cu
+int attn_fwd2_dispatch(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t s);
+
+}  // namespace attn
+}  // namespace dla

@@ -261,7 +261,7 @@ class Engine(ParamProvider):
         if unit in self._views:
             return self._views[unit]
         if self.full.get(unit) is None and self.fused_stream:
-            return self._acquire_fused_stream(unit)
+            return self._acquire_fused_stream(unit, backward)
         if self.full.get(unit) is None:
             self._gather_async(unit)
             work, full = self._gather_work.pop(unit)
@@ -272,19 +272,29 @@ class Engine(ParamProvider):
                 self._gather_async(nxt)
         spec = self._by_name[unit]
         w = unit_views(self.full[unit], spec)
-        if self.trainable:
-            gb = self.gradbuf.get(unit)
-            if gb is None:
-                gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
-                self.gradbuf[unit] = gb
-            g = unit_views(gb, spec)
-            for k, t in w.items():
-                t.requires_grad_(True)
-                t._grad_slot = g[k]
+        self._attach_grad_slots(unit, w, backward)
         self._views[unit] = w
         return w
 
-    def _acquire_fused_stream(self, unit: str) -> Weights:
+    def _attach_grad_slots(self, unit: str, w: Weights, backward: bool) -> None:
+        """Point every parameter view at its slice of the unit's gradient bucket.  Streamed units get a bucket only
+        when a backward can follow (a checkpointed forward runs under no_grad and needs none); the bucket is
+        freed again once its reduce-scatter has been folded into the fp32 shard (``_drain``), so at most a few
+        unit-sized buckets are alive — not one per layer (141 GB at 70B)."""
+        if not self.trainable:
+            return
+        gb = self.gradbuf.get(unit)
+        if gb is None:
+            if not (backward or torch.is_grad_enabled()):
+                return
+            gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
+            self.gradbuf[unit] = gb
+        g = unit_views(gb, self._by_name[unit])
+        for k, t in w.items():
+            t.requires_grad_(True)
+            t._grad_slot = g[k]
+
+    def _acquire_fused_stream(self, unit: str, backward: bool = False) -> Weights:
         """Streamed unit, fused path (b): big 2-D weights are NOT gathered here — each carries an ``_ag`` ticket
         and the first GEMM that consumes it pulls its rows from the owners inside the kernel; only the small
         parameters (norms, biases) and non-GEMM tables are gathered up front by a plain peer-load kernel."""
@@ -306,15 +316,7 @@ class Engine(ParamProvider):
                 self.fc.gather_range(ptrs, full, S, o, end - o)
                 self.stats["allgather_bytes"] += (end - o) * _bytes(self.dtype)
         self.full[unit] = full
-        if self.trainable:
-            gb = self.gradbuf.get(unit)
-            if gb is None:
-                gb = torch.zeros(P, dtype=self.grad_dtype, device=self.device)
-                self.gradbuf[unit] = gb
-            g = unit_views(gb, spec)
-            for k, t in w.items():
-                t.requires_grad_(True)
-                t._grad_slot = g[k]
+        self._attach_grad_slots(unit, w, backward)
         self._views[unit] = w
         return w
 
@@ -370,7 +372,7 @@ class Engine(ParamProvider):
                 self.gradbuf[unit][self.r * S:(self.r + 1) * S].copy_(out)
             else:
                 self.gshard[unit].add_(out.float())
-                self.gradbuf[unit] = None
+                self.gradbuf[unit] = None           # streamed: the full-size bucket lives only until it is reduced
                 self._views.pop(unit, None)
 
     def finish_backward(self) -> None:
