@@ -186,20 +186,23 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         if (p.causal) lim = min(lim, q_idx + 1);
         limit = lim - kv0;
       }
-      // ---- pass 1: row maximum
-      float mx = -INFINITY;
+      // ---- pass 1: row maximum.  The four 32-column loads are in flight together (one wait), and four
+      // independent max chains keep the FMNMX latency off the critical path of this lone warp.
+      float mx;
+      {
+        uint32_t v[128];
 #pragma unroll
-      for (int ch = 0; ch < 4; ++ch) {
-        uint32_t v[32];
-        tc::tmem_ld_32x32(tS + ch * 32, v);
+        for (int ch = 0; ch < 4; ++ch) tc::tmem_ld_32x32(tS + ch * 32, v + ch * 32);
         tc::tmem_ld_wait();
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
         if (!need_mask) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+          for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, ch * 32 + i < limit ? __uint_as_float(v[i]) : -INFINITY);
+          for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], i < limit ? __uint_as_float(v[i]) : -INFINITY);
         }
+        mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       }
       mx *= scale2;
       // ---- move the reference only when it is far off; O and l follow
@@ -220,40 +223,40 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       }
       if (need) m_ref = mx;
       const float neg_m = (m_ref == -INFINITY) ? 0.f : -m_ref;
-      // ---- pass 2: P = exp2(S * scale2 - m_ref) -> bf16 pairs -> TMEM columns [0, 64) of S_x
-      float sum = 0.f;
+      // ---- pass 2: P = exp2(S * scale2 - m_ref) -> bf16 pairs -> TMEM columns [0, 64) of S_x.
+      // Both 64-column halves are requested up front; P of half 0 overwrites S[0,32) (already in registers),
+      // P of half 1 overwrites S[32,64).
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};
+      {
+        uint32_t v[128];
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t pk[32];
+        for (int ch = 0; ch < 4; ++ch) tc::tmem_ld_32x32(tS + ch * 32, v + ch * 32);
+        tc::tmem_ld_wait();
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-          const int ch = half * 2 + cc;
-          uint32_t v[32];
-          tc::tmem_ld_32x32(tS + ch * 32, v);
-          tc::tmem_ld_wait();
+        for (int half = 0; half < 2; ++half) {
+          uint32_t pk[32];
           if (!need_mask) {
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const float p0 = ex2_approx(fmaf(__uint_as_float(v[i]), scale2, neg_m));
-              const float p1 = ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale2, neg_m));
-              sum += p0 + p1;
-              pk[cc * 16 + (i >> 1)] = pack_bf16x2(p0, p1);
+            for (int i = 0; i < 64; i += 2) {
+              const float p0 = ex2_approx(fmaf(__uint_as_float(v[half * 64 + i]), scale2, neg_m));
+              const float p1 = ex2_approx(fmaf(__uint_as_float(v[half * 64 + i + 1]), scale2, neg_m));
+              s4[(i >> 1) & 3] += p0 + p1;
+              pk[i >> 1] = pack_bf16x2(p0, p1);
             }
           } else {
 #pragma unroll
-            for (int i = 0; i < 32; i += 2) {
-              const int c = ch * 32 + i;
-              const float p0 = c < limit ? ex2_approx(fmaf(__uint_as_float(v[i]), scale2, neg_m)) : 0.f;
-              const float p1 = c + 1 < limit ? ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale2, neg_m)) : 0.f;
-              sum += p0 + p1;
-              pk[cc * 16 + (i >> 1)] = pack_bf16x2(p0, p1);
+            for (int i = 0; i < 64; i += 2) {
+              const int c = half * 64 + i;
+              const float p0 = c < limit ? ex2_approx(fmaf(__uint_as_float(v[c]), scale2, neg_m)) : 0.f;
+              const float p1 = c + 1 < limit ? ex2_approx(fmaf(__uint_as_float(v[c + 1]), scale2, neg_m)) : 0.f;
+              s4[(i >> 1) & 3] += p0 + p1;
+              pk[i >> 1] = pack_bf16x2(p0, p1);
             }
           }
+          tc::tmem_st_32x32(tS + half * 32, pk);
         }
-        // columns [32 half, 32 half + 32) of P overwrite S columns that pass 2 has already consumed
-        // (half 0 rewrites S[0,32) after reading S[0,64); half 1 rewrites S[32,64) after reading everything)
-        tc::tmem_st_32x32(tS + half * 32, pk);
       }
+      const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       tc::tmem_st_wait();
       tc::tc_fence_before();
       tc::mbar_arrive(&p_full[x]);
@@ -283,10 +286,12 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       if (in_range) {
 #pragma unroll
         for (int c = 0; c < 32; c += 8) {
-          float f[8];
-#pragma unroll
-          for (int t = 0; t < 8; ++t) f[t] = __uint_as_float(o[c + t]) * inv;
-          st8(dst + ch * 32 + c, pack8(f));
+          const uint32_t w0 = pack_bf16x2(__uint_as_float(o[c]) * inv, __uint_as_float(o[c + 1]) * inv);
+          const uint32_t w1 = pack_bf16x2(__uint_as_float(o[c + 2]) * inv, __uint_as_float(o[c + 3]) * inv);
+          const uint32_t w2 = pack_bf16x2(__uint_as_float(o[c + 4]) * inv, __uint_as_float(o[c + 5]) * inv);
+          const uint32_t w3 = pack_bf16x2(__uint_as_float(o[c + 6]) * inv, __uint_as_float(o[c + 7]) * inv);
+          // one 16-byte store (the compiler split the struct store into four 4-byte ones)
+          asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(dst + ch * 32 + c), "r"(w0), "r"(w1), "r"(w2), "r"(w3) : "memory");
         }
       }
     }

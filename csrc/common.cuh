@@ -51,8 +51,18 @@ struct __align__(16) bf16x8 {
   bf162 v[4];
 };
 
-__device__ __forceinline__ bf16x8 ld8(const bf16* p) { return *reinterpret_cast<const bf16x8*>(p); }
-__device__ __forceinline__ void st8(bf16* p, const bf16x8& v) { *reinterpret_cast<bf16x8*>(p) = v; }
+// 16-byte accesses go through uint4: a struct copy of four bf162 members is split by nvcc into four 4-byte
+// LDG/STG (cuobjdump showed 676 STG.E vs 8 STG.E.128 in elementwise.o), which quadruples LSU wavefronts and
+// L2 write requests.
+__device__ __forceinline__ bf16x8 ld8(const bf16* p) {
+  const uint4 u = *reinterpret_cast<const uint4*>(p);
+  bf16x8 r;
+  *reinterpret_cast<uint4*>(&r) = u;
+  return r;
+}
+__device__ __forceinline__ void st8(bf16* p, const bf16x8& v) {
+  *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(&v);
+}
 
 // streaming (read-once) 16-byte load that does not pollute L1
 __device__ __forceinline__ bf16x8 ld8_stream(const bf16* p) {
