@@ -60,9 +60,11 @@ def dpo_step(policy: CausalLM, ref: CausalLM, batch: Dict[str, Dict[str, torch.T
     B = ch["input_ids"].shape[0]
     if concat:
         ids, mask = _cat_pairs(ch, rj, pad_id)
-        pol = sequence_logprobs(policy, ids, mask, reduction)
+        # frozen reference first: it does not depend on the optimizer update of the previous step, so it overlaps
+        # the side-stream AdamW / gradient exchange (Engine.optimizer_step) that the policy forward must wait for
         with torch.no_grad():
             rf = sequence_logprobs(ref, ids, mask, reduction)
+        pol = sequence_logprobs(policy, ids, mask, reduction)
         pol_pos, pol_neg, ref_pos, ref_neg = pol[:B], pol[B:], rf[:B], rf[B:]
     else:
         pol_pos = sequence_logprobs(policy, ch["input_ids"], ch["attention_mask"], reduction)

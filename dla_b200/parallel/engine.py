@@ -118,6 +118,12 @@ class Engine(ParamProvider):
         self._passes_expected = 1
         self._passes_seen: Dict[str, int] = {}
         self._plain_used: set = set()
+        # optimizer / next-forward overlap: the update runs on a side stream; a unit's first acquire waits for its event
+        import os as _os
+        self.overlap_optimizer = _os.environ.get("DLA_OVERLAP_OPT", "1") != "0"
+        self._opt_stream: Optional["torch.cuda.Stream"] = None
+        self._unit_ready: Dict[str, "torch.cuda.Event"] = {}
+        self._all_ready: Optional["torch.cuda.Event"] = None
         self.sync_grads = True          # False on non-boundary accumulation micro-steps (``no_sync``)
         self.step_count = 0
         self._sumsq = None
@@ -257,7 +263,30 @@ class Engine(ParamProvider):
         i = self._order.index(unit) + (-1 if backward else 1)
         return self._order[i] if 0 <= i < len(self._order) else None
 
+    def sync_optimizer(self) -> None:
+        """Order the current stream after every pending side-stream optimizer update (no host wait)."""
+        if not self._unit_ready and self._all_ready is None:
+            return
+        cur = torch.cuda.current_stream(self.device)
+        for e in self._unit_ready.values():
+            cur.wait_event(e)
+        self._unit_ready.clear()
+        if self._all_ready is not None:
+            cur.wait_event(self._all_ready)
+            self._all_ready = None
+
+    def _wait_unit(self, unit: str) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        e = self._unit_ready.pop(unit, None)
+        if e is not None:
+            cur.wait_event(e)
+        if self._all_ready is not None:
+            cur.wait_event(self._all_ready)
+            self._all_ready = None
+
     def acquire(self, unit: str, backward: bool = False) -> Weights:
+        if self._unit_ready or self._all_ready is not None:
+            self._wait_unit(unit)          # the side-stream AdamW of the previous step may still be writing this unit
         if unit in self._views:
             return self._views[unit]
         if self.full.get(unit) is None and self.fused_stream:
@@ -414,8 +443,23 @@ class Engine(ParamProvider):
         bc1, bc2 = 1 - b1 ** t, 1 - b2 ** t
         prescale = 1.0 / grad_divisor
         cuda = self.device.type == "cuda"
+        self.sync_optimizer()
+        overlap = cuda and self.overlap_optimizer and (self.W == 1 or self.fused)
+        if overlap and self._opt_stream is None:
+            self._opt_stream = torch.cuda.Stream(device=self.device)
         if self.fused:
-            return self._fused_optimizer_step(opt, lr, prescale, bc1, bc2)
+            if not overlap:
+                return self._fused_optimizer_step(opt, lr, prescale, bc1, bc2)
+            # the whole reduce / AdamW / push sequence moves to the side stream: it is NVLink- and HBM-bound and
+            # overlaps the next step's frozen-reference forward (tensor-bound); the first acquire of any policy
+            # unit orders the main stream after it
+            main = torch.cuda.current_stream(self.device)
+            self._opt_stream.wait_stream(main)
+            with torch.cuda.stream(self._opt_stream):
+                self._fused_optimizer_step(opt, lr, prescale, bc1, bc2)
+                self._all_ready = torch.cuda.Event()
+                self._all_ready.record(self._opt_stream)
+            return
         # ---- global grad norm -------------------------------------------------------
         if cuda:
             s = N.stream_ptr(self.device)
@@ -445,6 +489,25 @@ class Engine(ParamProvider):
                 coef = 0.0
             self.last_grad_norm = torch.tensor(norm)
         # ---- update -----------------------------------------------------------------
+        if overlap:
+            # AdamW is a pure HBM stream (28 B per parameter): run it unit by unit, in forward order, on the side
+            # stream while the main stream already runs the next step's reference forward; each unit's first
+            # acquire waits for that unit's event only
+            main = torch.cuda.current_stream(self.device)
+            self._opt_stream.wait_stream(main)
+            with torch.cuda.stream(self._opt_stream):
+                sp = N.stream_ptr(self.device)
+                for u in self.units:
+                    g = self._local_grad(u.name)
+                    sh = self.shard[u.name]
+                    N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]), N.ptr(g),
+                           N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef),
+                           prescale, int(g.dtype == torch.float32) | self._moment_flag, sp)
+                    self.gradbuf[u.name].zero_()
+                    e = torch.cuda.Event()
+                    e.record(self._opt_stream)
+                    self._unit_ready[u.name] = e
+            return
         for u in self.units:
             g = self._local_grad(u.name)
             sh = self.shard[u.name]
@@ -502,6 +565,8 @@ class Engine(ParamProvider):
         self.zero_grad()
 
     def zero_grad(self) -> None:
+        if torch.cuda.is_available() and self.device.type == "cuda" and torch.cuda.current_stream(self.device) != self._opt_stream:
+            self.sync_optimizer()
         for k, g in self.gradbuf.items():
             if g is not None:
                 g.zero_()
@@ -514,6 +579,7 @@ class Engine(ParamProvider):
 
     def gathered_unit(self, unit: str) -> Weights:
         """Full (unsharded) views of a unit's parameters for export; collective when sharded."""
+        self.sync_optimizer()
         if self.full.get(unit) is not None:
             return unit_views(self.full[unit], self._by_name[unit])
         full = torch.empty(self.P[unit], dtype=self.dtype, device=self.device)
@@ -522,6 +588,7 @@ class Engine(ParamProvider):
 
     def load_unit(self, unit: str, tensors: Dict[str, torch.Tensor]) -> None:
         """Overwrite named parameters of a unit from full-size tensors (every rank passes the same)."""
+        self.sync_optimizer()
         spec = self._by_name[unit]
         offs = spec.offsets()
         S = self.S[unit]
@@ -540,6 +607,7 @@ class Engine(ParamProvider):
 
     def shard_state(self) -> Dict[str, torch.Tensor]:
         """This rank's exact-resume state: fp32 master + Adam moments per unit."""
+        self.sync_optimizer()
         out: Dict[str, torch.Tensor] = {}
         for u in self.units:
             if self.trainable:
@@ -551,6 +619,7 @@ class Engine(ParamProvider):
         return out
 
     def load_shard_state(self, state: Dict[str, torch.Tensor], step_count: int) -> None:
+        self.sync_optimizer()
         for u in self.units:
             if self.trainable and f"{u.name}.master" in state:
                 self.master[u.name].copy_(state[f"{u.name}.master"])

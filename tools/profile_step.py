@@ -35,6 +35,8 @@ def step():
     policy.engine.optimizer_step(opt)
 
 
+step()
+policy.engine.auto_no_recompute(2 * 4 * 1024)     # same policy as bench.py: keep activations where HBM allows
 for _ in range(2):
     step()
 torch.cuda.synchronize()
@@ -45,12 +47,14 @@ agg = defaultdict(lambda: [0.0, 0])
 for ev in prof.events():
     if ev.device_type == torch.autograd.DeviceType.CUDA:
         name = ev.name
-        for key in ("gemm_kernel", "attn_fwd", "attn_bwd_kernel", "attn_bwd_prep", "attn_bwd_dq", "rmsnorm_fwd", "rmsnorm_bwd",
+        for key in ("gemm2_kernel", "gemm_kernel", "attn_fwd", "attn_bwd_kernel", "attn_bwd_prep", "attn_bwd_dq", "rmsnorm_fwd", "rmsnorm_bwd",
                     "colsum", "rope", "swiglu_fwd", "swiglu_bwd", "adamw", "sumsq", "embedding", "logprob_grad", "logprob_combine",
                     "Memset", "Memcpy", "elementwise", "fill", "copy"):
             if key in name:
                 if key == "gemm_kernel":
                     key = "gemm_logprob" if "ELi1E" in name or ", 1>" in name or "(int)1>" in name else "gemm_store"
+                elif key == "gemm2_kernel":
+                    key = "gemm_2cta"
                 name = key
                 break
         agg[name][0] += ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
