@@ -251,18 +251,17 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, co
 }
 
 // ------------------------------------------------------------------------------- RoPE
-__global__ void rope_kernel(bf16* __restrict__ x, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
-                            const int32_t* __restrict__ positions, int64_t M, int n_heads, int head_dim,
-                            int rot_dim, int64_t row_stride, float sign) {
+// grid: x over (head, 8-pair vector) of one token row, y over token rows (grid-stride): 32-bit index math only
+__global__ void __launch_bounds__(256)
+rope_kernel(bf16* __restrict__ x, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+            const int32_t* __restrict__ positions, int64_t M, int n_heads, int head_dim, int rot_dim, int64_t row_stride,
+            float sign) {
   const int half = rot_dim >> 1;
   const int vec_per_head = half >> 3;  // 8 pairs per work item
-  const int64_t total = M * n_heads * vec_per_head;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int vi = (int)(idx % vec_per_head);
-    const int64_t t = idx / vec_per_head;
-    const int h = (int)(t % n_heads);
-    const int64_t m = t / n_heads;
+  const int item = blockIdx.x * blockDim.x + threadIdx.x;
+  if (item >= n_heads * vec_per_head) return;
+  const int h = item / vec_per_head, vi = item - h * vec_per_head;
+  for (int64_t m = blockIdx.y; m < M; m += gridDim.y) {
     const int pos = positions[m];
     bf16* base = x + m * row_stride + (int64_t)h * head_dim + vi * 8;
     float a[8], b[8], c[8], s[8];
@@ -287,37 +286,36 @@ __global__ void rope_kernel(bf16* __restrict__ x, const float* __restrict__ cos_
 }
 
 // ------------------------------------------------------------------------------- SwiGLU / GELU
-__global__ void swiglu_fwd_kernel(const bf16* __restrict__ gu, bf16* __restrict__ h, int64_t M, int F) {
-  const int fv = F >> 3;
-  const int64_t total = M * fv;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t m = idx / fv;
-    const int c = (int)(idx % fv) * 8;
+// grid: x over 8-element vectors of a row, y over rows (grid-stride) — no 64-bit divisions per element; the
+// sigmoid uses the fast reciprocal (the result is rounded to bf16 anyway)
+__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+
+__global__ void __launch_bounds__(256)
+swiglu_fwd_kernel(const bf16* __restrict__ gu, bf16* __restrict__ h, int64_t M, int F) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= F) return;
+  for (int64_t m = blockIdx.y; m < M; m += gridDim.y) {
     float g[8], u[8], o[8];
     unpack8(ld8_stream(gu + m * 2 * F + c), g);
     unpack8(ld8_stream(gu + m * 2 * F + F + c), u);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = g[j] / (1.f + __expf(-g[j])) * u[j];
+    for (int j = 0; j < 8; ++j) o[j] = g[j] * fast_sigmoid(g[j]) * u[j];
     st8(h + m * F + c, pack8(o));
   }
 }
 
-__global__ void swiglu_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ gu,
-                                  bf16* __restrict__ dgu, int64_t M, int F) {
-  const int fv = F >> 3;
-  const int64_t total = M * fv;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t m = idx / fv;
-    const int c = (int)(idx % fv) * 8;
+__global__ void __launch_bounds__(256)
+swiglu_bwd_kernel(const bf16* __restrict__ dh, const bf16* __restrict__ gu, bf16* __restrict__ dgu, int64_t M, int F) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= F) return;
+  for (int64_t m = blockIdx.y; m < M; m += gridDim.y) {
     float g[8], u[8], d[8], dg[8], du[8];
     unpack8(ld8_stream(gu + m * 2 * F + c), g);
     unpack8(ld8_stream(gu + m * 2 * F + F + c), u);
     unpack8(ld8_stream(dh + m * F + c), d);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float sg = 1.f / (1.f + __expf(-g[j]));
+      const float sg = fast_sigmoid(g[j]);
       du[j] = d[j] * g[j] * sg;
       dg[j] = d[j] * u[j] * sg * (1.f + g[j] * (1.f - sg));
     }
@@ -561,8 +559,11 @@ int dla_rope_inplace(void* x, const float* cos_t, const float* sin_t, const int3
               "rope: rot_dim=%d must be a multiple of 16 and <= head_dim=%d", rot_dim, head_dim);
   const int64_t work = M * n_heads * (rot_dim / 16);
   if (work == 0) return 0;
-  rope_kernel<<<ew_grid(work, 256), 256, 0, (cudaStream_t)stream>>>((bf16*)x, cos_t, sin_t, positions, M, n_heads,
-                                                                   head_dim, rot_dim, row_stride, sign);
+  const int items = n_heads * (rot_dim / 16);
+  const int threads = items >= 256 ? 256 : ((items + 31) / 32) * 32;
+  const dim3 grid((items + threads - 1) / threads, (unsigned)(M < 32768 ? M : 32768));
+  rope_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>((bf16*)x, cos_t, sin_t, positions, M, n_heads, head_dim, rot_dim,
+                                                          row_stride, sign);
   return check_launch("rope");
 }
 
@@ -570,7 +571,8 @@ int dla_swiglu_fwd(const void* gu, void* h, int64_t M, int F, void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
   DLA_REQUIRE(F % 8 == 0, DLA_E_BADARG, "swiglu: F=%d must be a multiple of 8", F);
   if (M == 0) return 0;
-  swiglu_fwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)gu, (bf16*)h, M, F);
+  const dim3 grid((F / 8 + 255) / 256, (unsigned)(M < 32768 ? M : 32768));
+  swiglu_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)gu, (bf16*)h, M, F);
   return check_launch("swiglu_fwd");
 }
 
@@ -578,7 +580,8 @@ int dla_swiglu_bwd(const void* dh, const void* gu, void* dgu, int64_t M, int F, 
   if (int rc_ = ::dla::ensure_device()) return rc_;
   DLA_REQUIRE(F % 8 == 0, DLA_E_BADARG, "swiglu: F=%d must be a multiple of 8", F);
   if (M == 0) return 0;
-  swiglu_bwd_kernel<<<ew_grid(M * (F / 8), 256), 256, 0, (cudaStream_t)stream>>>((const bf16*)dh, (const bf16*)gu, (bf16*)dgu, M, F);
+  const dim3 grid((F / 8 + 255) / 256, (unsigned)(M < 32768 ? M : 32768));
+  swiglu_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)dh, (const bf16*)gu, (bf16*)dgu, M, F);
   return check_launch("swiglu_bwd");
 }
 

@@ -313,8 +313,7 @@ def _llama_layer(cfg: ModelConfig):
         qkv = F.rope_qkv(qkv, positions.reshape(-1), Hq, Hk, D, cfg.rope_theta, cfg.rot_dim or None,
                          max_pos=cfg.max_position_embeddings)
         qkv4 = qkv.view(B, T, Hq + 2 * Hk, D)
-        attn = F.attention(qkv4[:, :, :Hq], qkv4[:, :, Hq:Hq + Hk], qkv4[:, :, Hq + Hk:], seqlens=seqlens,
-                           causal=True, segment_ids=segment_ids)
+        attn = F.attention_qkv(qkv4, Hq, Hk, seqlens=seqlens, causal=True, segment_ids=segment_ids)
         a = F.linear(attn.reshape(B, T, Hq * D), w["wo"])
         x, h = F.add_rmsnorm(x, a, w["mlp_norm"], cfg.norm_eps)
         gu = F.linear(h, w["w_gu"])
@@ -334,8 +333,7 @@ def _gpt2_layer(cfg: ModelConfig):
             x = x + delta
         h = F.layernorm(x, w["ln1_w"], w["ln1_b"], cfg.norm_eps)
         qkv4 = F.linear(h, w["wqkv"], w["bqkv"]).view(B, T, 3 * Hh, D)
-        attn = F.attention(qkv4[:, :, :Hh], qkv4[:, :, Hh:2 * Hh], qkv4[:, :, 2 * Hh:], seqlens=seqlens, causal=True,
-                           segment_ids=segment_ids)
+        attn = F.attention_qkv(qkv4, Hh, Hh, seqlens=seqlens, causal=True, segment_ids=segment_ids)
         x = x + F.linear(attn.reshape(B, T, H), w["wo"], w["bo"])
         h = F.layernorm(x, w["ln2_w"], w["ln2_b"], cfg.norm_eps)
         m = F.linear(F.gelu_bias(F.linear(h, w["w_fc"]), w["b_fc"]), w["w_proj"], w["b_proj"])

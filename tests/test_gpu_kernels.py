@@ -302,6 +302,12 @@ def test_attention_fwd_bwd(native_lib, B, T, Hq, Hk, D, ragged):
     _rel(x.grad[:, :, :Hq], xr.grad[:, :, :Hq], 3e-2, what="dq")
     _rel(x.grad[:, :, Hq:Hq + Hk], xr.grad[:, :, Hq:Hq + Hk], 3e-2, what="dk")
     _rel(x.grad[:, :, Hq + Hk:], xr.grad[:, :, Hq + Hk:], 3e-2, what="dv")
+    # packed entry (one autograd input, packed gradient out): identical kernels, identical numbers
+    x2 = qkv.clone().requires_grad_()
+    o2 = F.attention_qkv(x2, Hq, Hk, seqlens=seqlens, causal=True)
+    assert torch.equal(o2, o)
+    o2.backward(g)
+    assert torch.equal(x2.grad, x.grad)
 
 
 def test_attention_separate_tensors(native_lib):
