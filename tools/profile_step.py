@@ -49,7 +49,7 @@ for ev in prof.events():
         name = ev.name
         for key in ("gemm2_kernel", "gemm_kernel", "attn_fwd", "attn_bwd_kernel", "attn_bwd_prep", "attn_bwd_dq", "rmsnorm_fwd", "rmsnorm_bwd",
                     "colsum", "rope", "swiglu_fwd", "swiglu_bwd", "adamw", "sumsq", "embedding", "logprob_grad", "logprob_combine",
-                    "Memset", "Memcpy", "elementwise", "fill", "copy"):
+                    "Memset", "Memcpy"):
             if key in name:
                 if key == "gemm_kernel":
                     key = "gemm_logprob" if "ELi1E" in name or ", 1>" in name or "(int)1>" in name else "gemm_store"
@@ -57,6 +57,10 @@ for ev in prof.events():
                     key = "gemm_2cta"
                 name = key
                 break
+        if "at::native" in name:       # keep the functor name: which PyTorch elementwise ops are left in the step
+            import re
+            mm = re.search(r"(\w+Functor|\w+_kernel_cuda|FillFunctor|direct_copy_kernel|CatArray\w*|reduce_kernel|index\w*)", name)
+            name = "torch:" + (mm.group(1) if mm else name[:60])
         agg[name][0] += ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
         agg[name][1] += 1
 rows = sorted(((k, v[0] / 1e3, v[1]) for k, v in agg.items()), key=lambda r: -r[1])
