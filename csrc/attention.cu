@@ -342,7 +342,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 7);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int j = blockIdx.x, hk = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, longest-processing-time first: kv tile 0 (most query tiles at or below it) of every (kv head, batch)
+  // runs before any kv tile 1, ...; the launch ends with the shortest CTAs
+  const int n_hb = p.Hk * p.B;
+  const int j = (int)blockIdx.x / n_hb, hb = (int)blockIdx.x % n_hb;
+  const int hk = hb % p.Hk, b = hb / p.Hk;
   const int G = p.Hq / p.Hk;
   const int kv0 = j * BKV;
   int len = p.T;
@@ -723,7 +727,7 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_acc = dq_acc;
   // contract: dq has q's strides, dk/dv have k/v's strides
   p.dk = (bf16*)dk; p.dv = (bf16*)dv; p.dkv_sb = kv_sb; p.dkv_st = kv_st; p.dkv_sh = kv_sh;
-  dim3 grid((T + BKV - 1) / BKV, Hk, B);
+  dim3 grid((unsigned)(((T + BKV - 1) / BKV) * Hk * B));
   if (D == 128) {
     constexpr int smem = 4 * 128 * 128 * 2 + 2 * 128 * 128 * 2 + 1024 + 256;
     static bool set = false;

@@ -54,8 +54,12 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   uint32_t* tmem_holder = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int pi = (int)gridDim.x - 1 - (int)blockIdx.x;     // heaviest (last) query tiles first
-  const int h = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, longest-processing-time first: ALL (head, batch) instances of the heaviest query-tile pair are
+  // scheduled before any lighter pair, so the tail of the launch consists of the shortest CTAs
+  const int n_pairs = (p.T + 255) >> 8, n_hb = p.Hq * p.B;
+  const int pi = n_pairs - 1 - (int)blockIdx.x / n_hb;
+  const int hb = (int)blockIdx.x % n_hb;
+  const int h = hb % p.Hq, b = hb / p.Hq;
   const int hk = h / (p.Hq / p.Hk);
   int len = p.T;
   if (p.seqlens != nullptr) len = min(len, p.seqlens[b]);
@@ -313,7 +317,7 @@ int launch_fwd2(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMa
     DLA_CUDA(cudaFuncSetAttribute(attn_fwd2_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     set = true;
   }
-  dim3 grid((p.T + 255) / 256, p.Hq, p.B);
+  dim3 grid((unsigned)(((p.T + 255) / 256) * p.Hq * p.B));
   attn_fwd2_kernel<HD><<<grid, kFwd2Threads, smem, s>>>(tmQ, tmK, tmV, p);
   return check_launch("attn_fwd2");
 }

@@ -156,8 +156,10 @@ class _ChunkedDistillKL(torch.autograd.Function):
         ht, wt = list(teachers[0::2]), list(teachers[1::2])
         M = hs.shape[0]
         dh = torch.empty_like(hs)
-        slot = getattr(ctx.wref, "_grad_slot", None)
+        slot, acc = F._slot_gemm(ctx.wref)
         dw = None if slot is not None else torch.zeros_like(ws)
+        if slot is None:
+            acc = True
         wtgt = slot if slot is not None else dw
         for s in range(0, M, chunk):
             e = min(s + chunk, M)
@@ -166,7 +168,8 @@ class _ChunkedDistillKL(torch.autograd.Function):
                 tls = [F.gemm(h_t[s:e], w_t, out_dtype=torch.float32) for h_t, w_t in zip(ht, wt)]
                 _, dl = F.distill_kl_rows(sl, tls, m[s:e] / denom * g, temperature, want_kl=False, want_grad=True)
                 F.gemm(dl, ws, b_mn=True, out=dh[s:e])
-                F.gemm(dl, hs[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=True)
+                F.gemm(dl, hs[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=acc)
+                acc = True
                 continue
             sl = hs[s:e].float() @ ws.float().t()
             sp = torch.softmax(sl / temperature, -1)
@@ -178,6 +181,9 @@ class _ChunkedDistillKL(torch.autograd.Function):
             tp = tp / len(ht)
             dl = ((sp - tp) * (m[s:e] / denom * g / temperature)[:, None]).to(hs.dtype)
             dh[s:e] = dl @ ws
+            if not acc:
+                wtgt.zero_()
+                acc = True
             wtgt.add_((dl.t() @ hs[s:e]).to(wtgt.dtype))
         return (dh, dw, None, None, None) + (None,) * len(teachers)
 

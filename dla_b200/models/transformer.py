@@ -219,6 +219,9 @@ def collect_autograd_grads(weights: Weights) -> None:
         if t.grad is not None:
             slot = getattr(t, "_grad_slot", None)
             if slot is not None:
+                if getattr(slot, "_fresh", False):      # lazily zeroed bucket slice (see ops.functional._slot_add)
+                    slot.zero_()
+                    slot._fresh = False
                 slot.add_(t.grad.to(slot.dtype))
                 t.grad = None
 

@@ -31,6 +31,33 @@ def _check_bf16(*ts: Optional[torch.Tensor]) -> None:
             raise TypeError(f"native kernels take bf16 tensors, got {t.dtype}")
 
 
+# ---- gradient slots ---------------------------------------------------------------------
+# A parameter view may carry ``_grad_slot``: its slice of the engine's flat gradient bucket.  The engine does not
+# memset 16 GB of buckets per step: slots that are always produced by a wgrad GEMM are only MARKED fresh
+# (``_fresh``), and the first GEMM of the step overwrites instead of accumulating.  Every other kind of writer
+# (adds, atomics, reductions) goes through ``_slot_add`` which zero-fills a fresh slot first.
+
+def _slot_add(param: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """Slot of ``param`` for an accumulating writer (or None)."""
+    slot = getattr(param, "_grad_slot", None) if param is not None else None
+    if slot is not None and getattr(slot, "_fresh", False):
+        slot.zero_()
+        slot._fresh = False
+    return slot
+
+
+def _slot_gemm(param: torch.Tensor) -> Tuple[Optional[torch.Tensor], bool]:
+    """``(slot, accumulate)`` for a wgrad GEMM that covers the whole slot: a fresh slot is overwritten."""
+    slot = getattr(param, "_grad_slot", None)
+    if slot is None:
+        return None, False
+    slot._ow = True                      # tells the engine this slot may be left un-zeroed
+    if getattr(slot, "_fresh", False):
+        slot._fresh = False
+        return slot, False
+    return slot, True
+
+
 # =======================================================================================
 # GEMM
 # =======================================================================================
@@ -155,14 +182,14 @@ class _Linear(Function):
         if ctx.needs_input_grad[0]:
             dx = gemm(dy2, w, b_mn=True).view(ctx.xshape)
         if ctx.needs_input_grad[1]:
-            slot = getattr(ctx.wref, "_grad_slot", None)
+            slot, acc = _slot_gemm(ctx.wref)
             if slot is not None:
-                gemm(dy2, x2, a_mn=True, b_mn=True, out=slot, accumulate=True)
+                gemm(dy2, x2, a_mn=True, b_mn=True, out=slot, accumulate=acc)
             else:
                 dw = gemm(dy2, x2, a_mn=True, b_mn=True)
         if ctx.has_bias and ctx.needs_input_grad[2]:
             b = ctx.bias_ref
-            slot = getattr(b, "_grad_slot", None)
+            slot = _slot_add(b)
             H = dy2.shape[1]
             scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * H * 4, dy2.device)
             if slot is not None:
@@ -213,7 +240,7 @@ class _AddRMSNorm(Function):
         dr2 = _c(dresid.reshape(M, H)) if dresid is not None else None
         dx = torch.empty_like(resid)
         scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * H * 4, resid.device)
-        slot = getattr(ctx.wref, "_grad_slot", None)
+        slot = _slot_add(ctx.wref)
         dw = None
         need_w = ctx.needs_input_grad[2]
         if need_w and slot is None:
@@ -260,8 +287,8 @@ class _LayerNorm(Function):
         dx = torch.empty_like(x2)
         scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * 2 * H * 4, x2.device)
         wref, bref = ctx.refs
-        wslot = getattr(wref, "_grad_slot", None)
-        bslot = getattr(bref, "_grad_slot", None) if bref is not None else None
+        wslot = _slot_add(wref)
+        bslot = _slot_add(bref)
         use_slots = wslot is not None and (bref is None or bslot is not None)
         dw = wslot if use_slots else torch.empty(H, dtype=BF16, device=x2.device)
         db = None
@@ -389,7 +416,7 @@ class _GeluBias(Function):
         if ctx.has_bias and ctx.needs_input_grad[1]:
             H = x2.shape[1]
             scratch = N.workspace("norm_bwd", N.norm_bwd_blocks() * H * 4, x2.device)
-            slot = getattr(ctx.bias_ref, "_grad_slot", None)
+            slot = _slot_add(ctx.bias_ref)
             if slot is not None:
                 N.call("dla_bias_grad", N.ptr(dx), N.ptr(slot), N.ptr(scratch), 1, x2.shape[0], H, _s(x2))
             else:
@@ -428,8 +455,8 @@ class _Embedding(Function):
         M, H, V, T = ctx.meta
         table, pos_table = ctx.refs
         d2 = _c(dout.reshape(M, H))
-        tslot = getattr(table, "_grad_slot", None)
-        pslot = getattr(pos_table, "_grad_slot", None) if pos_table is not None else None
+        tslot = _slot_add(table)
+        pslot = _slot_add(pos_table)
         dt = tslot if tslot is not None else torch.zeros(V, H, dtype=BF16, device=d2.device)
         dp = None
         if pos_table is not None:
@@ -599,10 +626,11 @@ class _LinearLogprob(Function):
         V = w.shape[0]
         g = _c(g.float())
         dh = torch.empty_like(h) if ctx.needs_input_grad[0] else None
-        slot = getattr(ctx.wref, "_grad_slot", None)
+        slot, acc = _slot_gemm(ctx.wref)
         dw = None
         if ctx.needs_input_grad[1] and slot is None:
             dw = torch.zeros_like(w)
+            acc = True
         wtgt = slot if slot is not None else dw
         Vp = (V + 7) // 8 * 8
         chunk = min(LOGPROB_BWD_CHUNK, M)
@@ -617,7 +645,8 @@ class _LinearLogprob(Function):
             if dh is not None:
                 gemm(dl, w, b_mn=True, out=dh[s:e])
             if wtgt is not None:
-                gemm(dl, h[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=True)
+                gemm(dl, h[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=acc)
+                acc = True               # later row chunks add to the first one
         return dh, dw, None
 
 
@@ -733,7 +762,7 @@ HEAD_MODES = {"last_token": 0, "mean": 1, "token": 2}
 
 def _grad_to(param: torch.Tensor, g32: torch.Tensor) -> Optional[torch.Tensor]:
     """Route an fp32 parameter gradient: into the engine's bucket view when the parameter has one."""
-    slot = getattr(param, "_grad_slot", None)
+    slot = _slot_add(param)
     if slot is not None:
         slot.add_(g32.view_as(slot).to(slot.dtype))
         return None

@@ -123,6 +123,8 @@ class Engine(ParamProvider):
         self.overlap_optimizer = _os.environ.get("DLA_OVERLAP_OPT", "1") != "0"
         self._opt_stream: Optional["torch.cuda.Stream"] = None
         self._unit_ready: Dict[str, "torch.cuda.Event"] = {}
+        self._slots: Dict[str, Weights] = {}
+        self.lazy_zero = _os.environ.get("DLA_LAZY_ZERO", "1") != "0"
         self._all_ready: Optional["torch.cuda.Event"] = None
         self.sync_grads = True          # False on non-boundary accumulation micro-steps (``no_sync``)
         self.step_count = 0
@@ -319,6 +321,8 @@ class Engine(ParamProvider):
             gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
             self.gradbuf[unit] = gb
         g = unit_views(gb, self._by_name[unit])
+        if self.resident:
+            self._slots[unit] = g          # persistent bucket: zero_grad may mark GEMM-fed slots fresh instead of clearing
         for k, t in w.items():
             t.requires_grad_(True)
             t._grad_slot = g[k]
@@ -368,6 +372,7 @@ class Engine(ParamProvider):
         self._passes_seen[unit] = 0
         if self.ctx.world_size == 1:
             return
+        self._materialize_fresh(unit)
         if self.resident:
             if self.sync_grads:
                 self._launch_reduce(unit)
@@ -413,6 +418,7 @@ class Engine(ParamProvider):
             self._passes_seen[unit] = self._passes_expected - 1
             self.grads_done(unit, self._views.get(unit, {}))
         self._plain_used.clear()
+        self._materialize_fresh()       # slices nobody wrote this step become real zeros before peers / reductions read them
         self._drain(0)
         if self.fused and self.sync_grads:
             self.fc.barrier(0)      # every rank's gradient buckets are complete before anyone reads them
@@ -444,6 +450,7 @@ class Engine(ParamProvider):
         prescale = 1.0 / grad_divisor
         cuda = self.device.type == "cuda"
         self.sync_optimizer()
+        self._materialize_fresh()
         overlap = cuda and self.overlap_optimizer and (self.W == 1 or self.fused)
         if overlap and self._opt_stream is None:
             self._opt_stream = torch.cuda.Stream(device=self.device)
@@ -503,7 +510,7 @@ class Engine(ParamProvider):
                     N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]), N.ptr(g),
                            N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef),
                            prescale, int(g.dtype == torch.float32) | self._moment_flag, sp)
-                    self.gradbuf[u.name].zero_()
+                    self._zero_unit(u.name)
                     e = torch.cuda.Event()
                     e.record(self._opt_stream)
                     self._unit_ready[u.name] = e
@@ -567,11 +574,36 @@ class Engine(ParamProvider):
     def zero_grad(self) -> None:
         if torch.cuda.is_available() and self.device.type == "cuda" and torch.cuda.current_stream(self.device) != self._opt_stream:
             self.sync_optimizer()
-        for k, g in self.gradbuf.items():
-            if g is not None:
-                g.zero_()
+        for k in self.gradbuf:
+            self._zero_unit(k)
         for g in self.gshard.values():
             g.zero_()
+
+    def _zero_unit(self, unit: str) -> None:
+        """Clear one gradient bucket.  On CUDA, slices that are always (over)written by a wgrad GEMM are only marked
+        fresh — the first GEMM of the next step stores instead of accumulating (``ops.functional._slot_gemm``) — so
+        a step does not memset the whole 2-bytes-per-parameter bucket (16 GB at Llama-3-8B); everything else
+        (norm weights, biases, embedding tables, padding) is zero-filled as before."""
+        gb = self.gradbuf.get(unit)
+        if gb is None:
+            return
+        slots = self._slots.get(unit) if (self.lazy_zero and self.device.type == "cuda") else None
+        if not slots or not any(getattr(t, "_ow", False) for t in slots.values()):
+            gb.zero_()
+            return
+        for t in slots.values():
+            if getattr(t, "_ow", False):
+                t._fresh = True
+            else:
+                t.zero_()
+
+    def _materialize_fresh(self, unit: Optional[str] = None) -> None:
+        """Slots still marked fresh received no gradient this step: make their zeros real before anything reads them."""
+        for name in ([unit] if unit is not None else list(self._slots)):
+            for t in (self._slots.get(name) or {}).values():
+                if getattr(t, "_fresh", False):
+                    t.zero_()
+                    t._fresh = False
 
     # ------------------------------------------------------------------ state access
     def num_params(self) -> int:
