@@ -167,13 +167,33 @@ def main() -> None:
     # ---- (1) device-timed ------------------------------------------------------------------------
     dev_batches = [to_dev(b) for b in host]
     torch.cuda.synchronize(dev)
+    kept = 0
     for i in range(Wm):
-        step_fn(dev_batches[i])
-        if i == 0 and args.impl == "own" and os.environ.get("DLA_BENCH_NO_RECOMPUTE", "auto") != "0":
+        try:
+            step_fn(dev_batches[i])
+        except torch.OutOfMemoryError:
+            # only reachable on a single GPU when the kept activations leave too little slack: drop a few layers
+            # back to recomputation and repeat this warm-up step (parameters were not touched yet)
+            if args.impl != "own" or world > 1 or kept == 0:
+                raise
+            kept = eng.set_no_recompute_layers(max(0, kept - 4))
+            eng.zero_grad()
+            torch.cuda.empty_cache()
+            step_fn(dev_batches[i])
+        if args.impl != "own" or os.environ.get("DLA_BENCH_NO_RECOMPUTE", "auto") == "0":
+            continue
+        if i == 0:
             # after the first step the allocator's steady state is known: spend the free HBM on keeping
             # activations of the last k layers (no recomputation there); nothing is skipped, only not redone
-            kept = eng.auto_no_recompute(2 * MB * T) if os.environ.get("DLA_BENCH_NO_RECOMPUTE", "auto") == "auto" \
-                else eng.set_no_recompute_layers(int(os.environ["DLA_BENCH_NO_RECOMPUTE"]))
+            kept = eng.auto_no_recompute(2 * MB * T, reserve_gb=float(os.environ.get("DLA_BENCH_RESERVE_GB", 7.5))) \
+                if os.environ.get("DLA_BENCH_NO_RECOMPUTE", "auto") == "auto" else eng.set_no_recompute_layers(int(os.environ["DLA_BENCH_NO_RECOMPUTE"]))
+            torch.cuda.reset_peak_memory_stats(dev)
+        elif i == 1 and kept > 0 and world == 1:
+            # one step ran with the kept activations: if the measured peak leaves under 3 GiB, give some back
+            total = torch.cuda.get_device_properties(dev).total_memory
+            slack = total - torch.cuda.max_memory_reserved(dev)
+            if slack < (3 << 30):
+                kept = eng.set_no_recompute_layers(max(0, kept - 2))
     sampler = ClockSampler(dev.index or 0)
     sync_all()
     sampler.start()

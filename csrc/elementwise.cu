@@ -15,20 +15,35 @@ __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ delta, const bf16* __restrict__ w,
                    bf16* __restrict__ resid_out, bf16* __restrict__ y, float* __restrict__ rstd,
                    int64_t M, int H, float eps) {
+  // One block per row at a time, rows strided over the grid.  The raw 16-byte vectors of the NEXT row are requested
+  // before the current row's reduction (two block-wide syncs) so the loads of one row overlap the reduce + store
+  // phase of the previous one; without that the memory system idled during every reduction.
   __shared__ float red[33];
   const int nvec = H >> 3;
-  for (int64_t row = blockIdx.x; row < M; row += gridDim.x) {
-    const bf16* xr = x + row * H;
+  bf16x8 nx[VPT], nd[VPT];
+  auto fetch = [&](int64_t row) {
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int c = i * kNormThreads + threadIdx.x;
+      if (c < nvec) {
+        nx[i] = ld8_stream(x + row * H + c * 8);
+        if (delta != nullptr) nd[i] = ld8_stream(delta + row * H + c * 8);
+      }
+    }
+  };
+  int64_t row = blockIdx.x;
+  if (row < M) fetch(row);
+  for (; row < M; row += gridDim.x) {
     float vals[VPT][8];
     float ss = 0.f;
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int c = i * kNormThreads + threadIdx.x;
       if (c < nvec) {
-        unpack8(ld8_stream(xr + c * 8), vals[i]);
+        unpack8(nx[i], vals[i]);
         if (delta != nullptr) {
           float d[8];
-          unpack8(ld8_stream(delta + row * H + c * 8), d);
+          unpack8(nd[i], d);
 #pragma unroll
           for (int j = 0; j < 8; ++j) vals[i][j] += d[j];
           if (resid_out != nullptr) {
@@ -41,6 +56,7 @@ rmsnorm_fwd_kernel(const bf16* __restrict__ x, const bf16* __restrict__ delta, c
         for (int j = 0; j < 8; ++j) ss += vals[i][j] * vals[i][j];
       }
     }
+    if (row + gridDim.x < M) fetch(row + gridDim.x);      // in flight during the reduction and the stores below
     ss = block_sum(ss, red);
     const float r = rsqrtf(ss / (float)H + eps);
     if (threadIdx.x == 0) rstd[row] = r;
@@ -76,16 +92,32 @@ rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, cons
     for (int j = 0; j < 8; ++j) dwacc[i][j] = 0.f;
     if (c < nvec) unpack8(ld8(w + c * 8), wv[i]);
   }
-  for (int64_t row = blockIdx.x; row < M; row += gridDim.x) {
+  // raw vectors of the next row are requested before this row's reduction (same scheme as the forward)
+  bf16x8 nx[VPT], ng[VPT], nr[VPT];
+  auto fetch = [&](int64_t row) {
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+      const int c = i * kNormThreads + threadIdx.x;
+      if (c < nvec) {
+        nx[i] = ld8_stream(x + row * H + c * 8);
+        ng[i] = ld8_stream(dy + row * H + c * 8);
+        if (dresid != nullptr) nr[i] = ld8_stream(dresid + row * H + c * 8);
+      }
+    }
+  };
+  int64_t row = blockIdx.x;
+  if (row < M) fetch(row);
+  for (; row < M; row += gridDim.x) {
     const float r = rstd[row];
-    float xh[VPT][8], g[VPT][8];
+    float xh[VPT][8], g[VPT][8], dres[VPT][8];
     float dot = 0.f;
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
       const int c = i * kNormThreads + threadIdx.x;
       if (c < nvec) {
-        unpack8(ld8_stream(x + row * H + c * 8), xh[i]);
-        unpack8(ld8_stream(dy + row * H + c * 8), g[i]);
+        unpack8(nx[i], xh[i]);
+        unpack8(ng[i], g[i]);
+        if (dresid != nullptr) unpack8(nr[i], dres[i]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[i][j] *= r;
@@ -95,6 +127,7 @@ rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, cons
         }
       }
     }
+    if (row + gridDim.x < M) fetch(row + gridDim.x);
     dot = block_sum(dot, red) / (float)H;
 #pragma unroll
     for (int i = 0; i < VPT; ++i) {
@@ -104,10 +137,8 @@ rmsnorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, cons
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = r * (g[i][j] - xh[i][j] * dot);
         if (dresid != nullptr) {
-          float d[8];
-          unpack8(ld8_stream(dresid + row * H + c * 8), d);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) o[j] += d[j];
+          for (int j = 0; j < 8; ++j) o[j] += dres[i][j];
         }
         st8(dx + row * H + c * 8, pack8(o));
       }
