@@ -82,16 +82,20 @@ decode_attn_kernel(bf16* __restrict__ qkv, int64_t qkv_stride, bf16* __restrict_
     vc[(((int64_t)b * S_max + pos) * Hk + hk) * HD + i] = row[(int64_t)(Hq + Hk + hk) * HD + i];
   __syncthreads();      // cache row and q_s visible to the whole block
 
-  // ---- 2. scores: one cache position per lane -------------------------------------------------------------
+  // ---- 2. scores: one cache position per thread.  All 2*HD bytes of the K row are requested before the first FMA
+  // (one L2 round trip per position instead of one per 16-byte chunk).
   for (int s = tid; s < len; s += kThreads) {
-    const bf16x8* kp = reinterpret_cast<const bf16x8*>(kc + (((int64_t)b * S_max + s) * Hk + hk) * HD);
+    const bf16* kp = kc + (((int64_t)b * S_max + s) * Hk + hk) * HD;
+    bf16x8 kraw[HD / 8];
+#pragma unroll
+    for (int c = 0; c < HD / 8; ++c) kraw[c] = ld8(kp + c * 8);
     float d[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) d[g] = 0.f;
-#pragma unroll 4
+#pragma unroll
     for (int c = 0; c < HD / 8; ++c) {
       float kv[8];
-      unpack8(kp[c], kv);
+      unpack8(kraw[c], kv);
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         const float4 qa = *reinterpret_cast<const float4*>(q_s + g * HD + c * 8);
@@ -130,14 +134,28 @@ decode_attn_kernel(bf16* __restrict__ qkv, int64_t qkv_stride, bf16* __restrict_
   for (int g = 0; g < G; ++g)
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
-  for (int s = stripe; s < len; s += kStripes) {
-    float vv[8];
-    unpack8(ld8(vc + (((int64_t)b * S_max + s) * Hk + hk) * HD + ch * 8), vv);
+  // positions of this stripe in batches of kBatch independent 16-byte loads
+  constexpr int kBatch = 8;
+  for (int s0 = stripe; s0 < len; s0 += kStripes * kBatch) {
+    bf16x8 raw[kBatch];
 #pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const float pr = sc[(size_t)g * S_max + s];
+    for (int u = 0; u < kBatch; ++u) {
+      const int s = s0 + u * kStripes;
+      if (s < len) raw[u] = ld8(vc + (((int64_t)b * S_max + s) * Hk + hk) * HD + ch * 8);
+    }
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[g][e] += pr * vv[e];
+    for (int u = 0; u < kBatch; ++u) {
+      const int s = s0 + u * kStripes;
+      if (s < len) {
+        float vv[8];
+        unpack8(raw[u], vv);
+#pragma unroll
+        for (int g = 0; g < G; ++g) {
+          const float pr = sc[(size_t)g * S_max + s];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[g][e] += pr * vv[e];
+        }
+      }
     }
   }
 #pragma unroll

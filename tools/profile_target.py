@@ -27,6 +27,21 @@ elif what in ("attn_fwd", "attn_bwd"):
         o = F.attention(q, k, v)
         if what == "attn_bwd":
             torch.autograd.grad(o, qkv, r(B, T, Hq, D))
+elif what == "skinny":
+    x, w = r(8, 4096), r(28672, 4096)
+    for _ in range(3):
+        y = F.gemm(x, w)
+elif what == "decode_attn":
+    from dla_b200.ops import native as N
+    B, S, Hq, Hk, D = 8, 320, 32, 8, 128
+    qkv = r(B, (Hq + 2 * Hk) * D)
+    kc, vc = r(B, S, Hk, D), r(B, S, Hk, D)
+    lens = torch.full((B,), 300, device=dev, dtype=torch.int32)
+    cos, sin = F.rope_tables(8192, D, 500000.0, torch.device(dev))
+    o = torch.empty(B, Hq, D, device=dev, dtype=torch.bfloat16)
+    for _ in range(3):
+        N.call("dla_decode_attn_fused", N.ptr(qkv), qkv.stride(0), N.ptr(kc), N.ptr(vc), N.ptr(o), N.ptr(lens), N.ptr(cos), N.ptr(sin),
+               B, S, Hq, Hk, D, D, D ** -0.5, N.stream_ptr())
 elif what == "lmhead":
     h, w = r(4096, 4096), r(128256, 4096) * 0.02
     lab = torch.randint(0, 128256, (4096,), device=dev)
