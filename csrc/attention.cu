@@ -435,6 +435,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           tc::umma_bf16<1>(tmem_dK, tc::make_smem_desc(adS + ks * 2048, 16384, 1024),
                            tc::make_smem_desc(aQ + ks * 2048, 16384, 1024), idesc_t, (it > 0 || ks > 0) ? 1u : 0u);
         }
+        // Q and dO are dead once dV / dK retire: release them now so the TMA load of the next query tile overlaps the
+        // dQ MMA and its epilogue (there is no shared memory left for a second Q/dO stage)
+        tc::umma_commit(qdo_empty);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {   // dQ = dS K : contraction over the 128 kv rows
           const uint32_t off = (ks >> 2) * 16384 + (ks & 3) * 32;
@@ -442,7 +445,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                            idesc_q, ks > 0 ? 1u : 0u);
         }
         tc::umma_commit(dq_full);
-        tc::umma_commit(qdo_empty);
       }
     }
   } else {
