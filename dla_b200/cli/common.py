@@ -51,7 +51,7 @@ class TrainLoop:
                  tokens_fn: Optional[Callable[[Any], int]] = None, flops_per_token: float = 0.0) -> None:
         self.cfg, self.phase, self.ctx, self.plan = cfg, phase, ctx, plan
         self.engine, self.engines, self.tokenizer, self.opt = engine, engines, tokenizer, opt
-        self.total_steps, self.log_every, self.save_every = int(total_steps), int(log_every), int(save_every)
+        self.total_steps, self.log_every, self.save_every = int(total_steps), max(1, int(log_every)), int(save_every)
         self.scheduler, self.warmup = scheduler, int(warmup_steps)
         log_cfg = cfg.get("logging", {}) or {}
         self.output_dir = log_cfg.get("output_dir", f"checkpoints/{phase}")

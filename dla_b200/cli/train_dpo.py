@@ -74,7 +74,7 @@ def main() -> None:
 
         loss = loop.micro_step(loss_fn, batch)
         extra = None
-        if loop.global_step % eval_every == 0:
+        if eval_every > 0 and loop.global_step % eval_every == 0:
             extra = {"train/preference_rate": float(info["preference_rate"].item()), "train/margin": float(info["margin"].item())}
             loop.logger.log(extra, loop.global_step)
         loop.after_step(loss, sampler=sampler)

@@ -77,7 +77,7 @@ def main() -> None:
         loop.epoch = epoch
         loss = loop.micro_step(lambda: reward_step(model, batch, concat=concat, pad_id=pad_id)[0], batch)
         loop.after_step(loss, sampler=sampler)
-        if eval_loader is not None and loop.global_step % eval_every == 0:
+        if eval_loader is not None and eval_every > 0 and loop.global_step % eval_every == 0:
             m = evaluate(model, eval_loader, ctx)
             loop.logger.log({"eval/loss": m["loss"], "eval/acc": m["accuracy"]}, loop.global_step)
             ctx.print0(f"[reward] step {loop.global_step} eval/loss {m['loss']:.4f} eval/acc {m['accuracy']:.3f}")

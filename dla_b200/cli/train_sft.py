@@ -73,7 +73,7 @@ def main() -> None:
         loop.epoch = epoch
         loss = loop.micro_step(lambda: sft_loss(bundle.model, batch), batch)
         loop.after_step(loss, sampler=sampler)
-        if eval_loader is not None and loop.global_step % eval_every == 0:
+        if eval_loader is not None and eval_every > 0 and loop.global_step % eval_every == 0:
             ev = evaluate_loss(bundle.model, eval_loader, ctx)
             loop.logger.log({"eval/loss": ev}, loop.global_step)
             ctx.print0(f"[sft] step {loop.global_step} eval/loss {ev:.4f}")
