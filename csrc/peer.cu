@@ -280,6 +280,42 @@ fused_gather_dpo_kernel(float* const* peer_bufs, uint32_t* const* pads, int worl
   }
 }
 
+// Tiny all-gather (eval losses, per-rank statistics): every rank stores its n floats into slot `me`
+// of every peer's buffer, flags are exchanged, then the world x n block is copied out.  bufs[r]: fp32
+// [2][world][nmax] on rank r — the half is chosen by the epoch parity, so a fast rank that already entered the
+// next call writes the other half while a slow one still reads (nobody can be two calls ahead of a peer: the flag
+// exchange of call k+1 needs every rank to have finished call k).  Single block.
+__global__ void __launch_bounds__(256)
+peer_allgather_small_kernel(float* const* bufs, uint32_t* const* pads, int world, int me, const float* src, int n, int nmax,
+                            uint32_t epoch, int channel, long long timeout_cycles, float* out) {
+  __shared__ int s_ok;
+  const int64_t half = (int64_t)(epoch & 1u) * world * nmax;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = src[i];
+    for (int r = 0; r < world; ++r) {
+      float* dst = bufs[r] + half + (int64_t)me * nmax + i;
+      asm volatile("st.global.relaxed.sys.f32 [%0], %1;" ::"l"(dst), "f"(v) : "memory");
+    }
+  }
+  __syncthreads();
+  const bool ok = barrier_body(pads, world, me, channel, epoch, timeout_cycles);
+  if (threadIdx.x == 0) s_ok = 1;
+  __syncthreads();
+  if (!ok) s_ok = 0;
+  __syncthreads();
+  if (!s_ok) {
+    if (threadIdx.x == 0) atomicExch(&g_peer_timeout_flag, 1u);
+    return;
+  }
+  const float* mine = bufs[me] + half;
+  for (int idx = threadIdx.x; idx < world * n; idx += blockDim.x) {
+    const int r = idx / n, i = idx - r * n;
+    float v;
+    asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(v) : "l"(mine + (int64_t)r * nmax + i) : "memory");
+    out[idx] = v;
+  }
+}
+
 static long long timeout_cycles(int timeout_ms) {
   return timeout_ms > 0 ? (long long)timeout_ms * 1900000LL : 0;   // ~1.9 GHz SM clock
 }
@@ -382,6 +418,16 @@ int dla_fused_gather_dpo(float* const* peer_bufs, uint32_t* const* pads, int wor
                                                               1024, beta, label_smoothing, epoch, /*channel=*/1,
                                                               timeout_cycles(20000), out, dpol_pos, dpol_neg, nullptr);
   return check_launch("fused_gather_dpo");
+}
+
+int dla_peer_allgather_small(float* const* bufs, uint32_t* const* pads, int world, int rank, const float* src, int n, int nmax,
+                             uint32_t epoch, int channel, float* out, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world && n > 0 && n <= nmax, DLA_E_BADARG,
+              "peer_allgather_small: bad world/rank/n %d/%d/%d (nmax %d)", world, rank, n, nmax);
+  peer_allgather_small_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(bufs, pads, world, rank, src, n, nmax, epoch, channel,
+                                                                  timeout_cycles(20000), out);
+  return check_launch("peer_allgather_small");
 }
 
 }  // extern "C"

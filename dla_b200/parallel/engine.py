@@ -130,7 +130,7 @@ class Engine(ParamProvider):
         self.step_count = 0
         self._sumsq = None
         self._coef = None
-        self.last_grad_norm: Optional[torch.Tensor] = None
+        self._last_grad_norm: Optional[torch.Tensor] = None
         self.stats = {"allgather_bytes": 0, "reduce_bytes": 0}
         self._build(seed, init)
 
@@ -264,6 +264,14 @@ class Engine(ParamProvider):
     def _neighbour(self, unit: str, backward: bool) -> Optional[str]:
         i = self._order.index(unit) + (-1 if backward else 1)
         return self._order[i] if 0 <= i < len(self._order) else None
+
+    @property
+    def last_grad_norm(self) -> Optional[torch.Tensor]:
+        """Global gradient norm of the last optimizer step (device scalar).  With the fused path the value is produced
+        on the optimizer side stream, so the reader's stream is ordered after it first."""
+        if self.device.type == "cuda":
+            self.sync_optimizer()
+        return self._last_grad_norm
 
     def sync_optimizer(self) -> None:
         """Order the current stream after every pending side-stream optimizer update (no host wait)."""
@@ -479,7 +487,7 @@ class Engine(ParamProvider):
                 dist.all_reduce(self._sumsq, group=self.ctx.group)
             self._sumsq.mul_(prescale * prescale)
             N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
-            self.last_grad_norm = self._norm
+            self._last_grad_norm = self._norm
         else:
             sq = torch.zeros((), dtype=torch.float64)
             for u in self.units:
@@ -494,7 +502,7 @@ class Engine(ParamProvider):
                 coef = min(1.0, opt.max_grad_norm / (norm + 1e-6))
             if not math.isfinite(norm):
                 coef = 0.0
-            self.last_grad_norm = torch.tensor(norm)
+            self._last_grad_norm = torch.tensor(norm)
         # ---- update -----------------------------------------------------------------
         if overlap:
             # AdamW is a pure HBM stream (28 B per parameter): run it unit by unit, in forward order, on the side
@@ -554,7 +562,7 @@ class Engine(ParamProvider):
                 self.stats["reduce_bytes"] += self.S[u.name] * _bytes(self.grad_dtype) * (self.W - 1)
             dist.all_reduce(self._sumsq, group=self.ctx.group)
             N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
-            self.last_grad_norm = self._norm
+            self._last_grad_norm = self._norm
             for u in self.units:
                 sh, off = self.shard[u.name], self.base[u.name] + self.r * self.S[u.name]
                 N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]),
@@ -567,7 +575,7 @@ class Engine(ParamProvider):
                 off = self.base[u.name] + self.r * self.S[u.name]
                 fc.reduce_adamw_push(self.grad_arena, self.param_arena, off, self.S[u.name], prescale, self.master[u.name],
                                      self.m[u.name], self.v[u.name], lr, (b1, b2), opt.eps, opt.weight_decay, bc1, bc2, None)
-            self.last_grad_norm = None
+            self._last_grad_norm = None
         fc.barrier(0)               # all peers finished reading my gradients and writing my parameters
         self.zero_grad()
 

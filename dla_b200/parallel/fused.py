@@ -22,6 +22,7 @@ from dla_b200.ops import native as N
 from dla_b200.parallel.pg import DistContext
 
 PAD_WORDS = 4096           # uint32 flag words per rank (channels x world)
+GATHER_NMAX = 2048
 DPO_BMAX = 1024
 
 
@@ -61,7 +62,9 @@ class FusedComm:
         self.W, self.r = ctx.world_size, ctx.rank
         self.pads = SymmetricArena(ctx, PAD_WORDS, torch.int32)
         self.dpo_buf = SymmetricArena(ctx, self.W * 4 * DPO_BMAX, torch.float32)
+        self.gather_buf = SymmetricArena(ctx, 2 * self.W * GATHER_NMAX, torch.float32)
         self._epoch = [0] * 8
+        ctx.fused_comm = self           # DistContext.gather routes small CUDA tensors through all_gather_small
 
     @classmethod
     def get(cls, ctx: DistContext) -> "FusedComm":
@@ -126,6 +129,18 @@ class FusedComm:
         N.call("dla_ag_gemm_bf16", N.ptr(x2), N.ptr(unit_ptrs), N.ptr(full), shard_elems, b_offset, N.ptr(y), M, n_out, K,
                x2.stride(0), y.stride(0), self.W, self.r, N.ptr(flags), epoch, n_copy, 0, N.stream_ptr(x2.device))
         return y
+
+    def all_gather_small(self, x: torch.Tensor) -> torch.Tensor:
+        """``[world, n]`` fp32 gather of a small fp32 vector (n <= GATHER_NMAX) in one single-block kernel over peer
+        memory: stores into every peer's slot, flag exchange, copy-out (eval losses / logged statistics)."""
+        x = x.detach().float().contiguous().view(-1)
+        n = x.numel()
+        assert 0 < n <= GATHER_NMAX
+        out = torch.empty(self.W, n, dtype=torch.float32, device=x.device)
+        self._epoch[3] += 1
+        N.call("dla_peer_allgather_small", self.gather_buf.ptrs_dev, self.pads.ptrs_dev, self.W, self.r, N.ptr(x), n, GATHER_NMAX,
+               self._epoch[3], 3, N.ptr(out), N.stream_ptr(x.device))
+        return out
 
     # ---------------------------------------------------------------- (c)
     def dpo_loss(self, pol_pos, pol_neg, ref_pos, ref_neg, beta: float, label_smoothing: float):

@@ -26,6 +26,7 @@ class DistContext:
     device: torch.device = torch.device("cpu")
     backend: str = "none"
     group: Optional[Any] = None
+    fused_comm: Optional[Any] = None       # set by parallel.fused.FusedComm: peer-memory path for tiny collectives
 
     @property
     def is_main(self) -> bool:
@@ -59,6 +60,10 @@ class DistContext:
         if not self.distributed:
             return t
         t = t.contiguous()
+        fc = self.fused_comm
+        if fc is not None and t.is_cuda and t.is_floating_point() and 0 < t.numel() <= 2048 and t.dim() >= 1:
+            # eval losses / logged statistics: one single-block peer-memory kernel instead of an NCCL launch
+            return fc.all_gather_small(t).to(t.dtype).view((self.world_size * t.shape[0],) + tuple(t.shape[1:]))
         out = torch.empty((self.world_size * t.shape[0],) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
         dist.all_gather_into_tensor(out, t, group=self.group)
         return out

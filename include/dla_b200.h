@@ -303,6 +303,12 @@ int dla_fused_gather_dpo(float* const* peer_bufs, uint32_t* const* pads, int wor
                          const float* ref_neg, int B, float beta, float label_smoothing,
                          uint32_t epoch, float* out, float* dpol_pos, float* dpol_neg, void* stream);
 
+/* Tiny all-gather over peer memory (eval losses, per-rank statistics): out[r*n + i] = rank r's src[i].  bufs: device
+ * array of per-rank fp32 buffers [2][world][nmax] (the half is picked by the epoch parity); pads/channel/epoch as
+ * for dla_peer_barrier.  R: accelerator.gather at R/src/training/train_sft.py:39, train_reward.py:47. */
+int dla_peer_allgather_small(float* const* bufs, uint32_t* const* pads, int world, int rank, const float* src, int n,
+                             int nmax, uint32_t epoch, int channel, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -90,6 +90,20 @@ def _kernels_worker(rank, world, port):
     assert torch.allclose(stats[0], want_loss, atol=1e-5)
     assert torch.allclose(stats[1], (allv[0] > allv[1]).float().mean(), atol=1e-6)
     assert torch.allclose(dpp, a.grad, atol=1e-6) and torch.allclose(dpn, b.grad, atol=1e-6)
+    # ---- tiny all-gather over peer memory (ctx.gather routes through it once a FusedComm exists) vs NCCL,
+    # several calls back to back with changing sizes (the buffer halves alternate with the epoch parity)
+    assert ctx.fused_comm is fc
+    for it, n in enumerate([1, 7, 2048, 3, 64, 1]):
+        x = torch.randn(n, device=dev, generator=g) + 10 * rank + it
+        got = ctx.gather(x)
+        want_g = torch.empty(world * n, device=dev)
+        dist.all_gather_into_tensor(want_g, x, group=ctx.group)
+        assert torch.equal(got, want_g), (it, n)
+    xb = torch.randn(4, 3, device=dev, generator=g).to(torch.bfloat16)
+    got = ctx.gather(xb)
+    want_b = torch.empty(world * 4, 3, device=dev, dtype=torch.bfloat16)
+    dist.all_gather_into_tensor(want_b, xb, group=ctx.group)
+    assert got.dtype == torch.bfloat16 and torch.equal(got, want_b)
     fc.check()
     ctx.barrier()
 
