@@ -112,4 +112,28 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
   return t;
 }
 
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------------------------
+// A kernel launched with launch_pdl may become resident while its stream predecessor is still running; it must
+// execute pdl_wait() before touching anything the predecessor produces (the wait returns once the predecessor grid
+// has completed and flushed).  pdl_launch_dependents() lets the successor start its own pre-wait prologue early.
+// Both are no-ops for kernels launched the ordinary way.  Used along the decode chain (one token = ~260 short
+// dependent kernels), where launch latency and ramp-up would otherwise be paid between every pair.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace dla
