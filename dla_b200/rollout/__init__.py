@@ -371,6 +371,46 @@ class Generator:
         return GenerationOutput(seqs, amask, plen.long(), rmask, lens.long())
 
 
+class GraphedForward:
+    """``model.logits(ids, mask)`` for one fixed ``[B, S]`` shape, captured once and replayed as a single CUDA graph.
+
+    A prefill of a few hundred tokens is launch-bound (≈330 launches of 5-30 us each for Llama-3-8B): serving and the
+    latency grid (``R/src/eval/eval_latency.py:42-53`` runs the same shape ``measure_steps`` times) replay the graph
+    instead.  Inputs are copied into fixed buffers; the returned logits tensor is the graph's output buffer (valid
+    until the next call).  Requires resident parameters (acquiring a unit must not launch collectives)."""
+
+    def __init__(self, model: CausalLM, batch: int, seq: int, last_only: bool = False) -> None:
+        import gc
+
+        dev = model.p.device if hasattr(model.p, "device") else torch.device("cuda")
+        self.ids = torch.zeros(batch, seq, dtype=torch.long, device=dev)
+        self.mask = torch.ones(batch, seq, dtype=torch.long, device=dev)
+        with torch.no_grad(), F.weights_static():
+            for _ in range(2):                       # work areas, function attributes and device binding exist before capture
+                model.logits(self.ids, self.mask, last_only=last_only)
+            torch.cuda.synchronize(dev)
+            gc.collect()
+            was = gc.isenabled()
+            gc.disable()                             # a dead CUDA graph freed mid-capture would invalidate this capture
+            try:
+                self.graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(self.graph):
+                    self.out = model.logits(self.ids, self.mask, last_only=last_only)
+            finally:
+                if was:
+                    gc.enable()
+
+    @torch.no_grad()
+    def __call__(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        self.ids.copy_(input_ids)
+        if attention_mask is not None:
+            self.mask.copy_(attention_mask)
+        else:
+            self.mask.fill_(1)
+        self.graph.replay()
+        return self.out
+
+
 def sample(logits: torch.Tensor, temperature: float, top_p: float, generator: Optional[torch.Generator] = None,
            seed: int = 0, step: int = 0, step_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Next-token choice on the device: greedy when ``temperature <= 0`` else nucleus sampling.  CUDA runs

@@ -135,3 +135,23 @@ def test_rlhf_reinforce_and_ppo_steps_run(native_lib, ctx):
     pol.engine.finish_backward()
     pol.engine.optimizer_step(AdamWConfig(lr=1e-4))
     assert torch.isfinite(l2) and float(st["approx_kl"]) < 1e-3
+
+
+def test_graphed_prefill_forward_matches_eager(native_lib, ctx):
+    """GraphedForward replays model.logits for a fixed [B, S]: same numbers as the eager launch sequence, for new inputs
+    and padding masks copied into its fixed buffers."""
+    from dla_b200.models.factory import load_causal_lm
+    from dla_b200.rollout import GraphedForward
+
+    b = load_causal_lm("tiny-llama", ctx, trainable=False, gradient_checkpointing=False, seed=7)
+    gf = GraphedForward(b.model, 3, 40)
+    for seed in (1, 2):
+        torch.manual_seed(seed)
+        ids = torch.randint(4, 500, (3, 40), device="cuda")
+        mask = torch.ones_like(ids)
+        mask[1, 25:] = 0
+        with torch.no_grad():
+            want = b.model.logits(ids, mask)
+        got = gf(ids, mask)
+        valid = mask.bool()
+        assert torch.equal(got[valid], want[valid]), seed

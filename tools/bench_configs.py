@@ -131,9 +131,17 @@ elif args.what == "latency":
     if args.impl == "own":
         from dla_b200.models.factory import load_causal_lm
 
+        from dla_b200.rollout import GraphedForward
+
         b = load_causal_lm(args.model, ctx, trainable=False, gradient_checkpointing=False, name="lat")
         V = b.config.vocab_size
-        fwd = lambda ids, mask: b.model.logits(ids, mask)
+        graphs = {}
+
+        def fwd(ids, mask):          # one captured graph per [B, S], as dla_b200.cli.eval_latency does
+            key = tuple(ids.shape)
+            if key not in graphs:
+                graphs[key] = GraphedForward(b.model, *key)
+            return graphs[key](ids, mask)
     else:
         m = hf_model(False)
         V = m.config.vocab_size
