@@ -14,8 +14,13 @@ import yaml
 ROOT = Path(__file__).resolve().parents[1]
 
 
+_DEVICE = ["cpu"]        # the chain below runs once on CPU and once (marked gpu) on a CUDA device
+
+
 def _run(module, *args, timeout=600):
-    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="")
+    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="2")
+    if _DEVICE[0] == "cpu":
+        env["CUDA_VISIBLE_DEVICES"] = ""
     res = subprocess.run([sys.executable, "-m", module, *args], cwd=ROOT, env=env, capture_output=True, text=True, timeout=timeout)
     assert res.returncode == 0, f"{module} failed:\n{res.stdout[-3000:]}\n{res.stderr[-3000:]}"
     return res.stdout
@@ -45,10 +50,16 @@ def _log(d: Path, phase: str, **kw):
     return base
 
 
-@pytest.mark.timeout(900)
-def test_phase_chain(work):
-    d = work
-    hw = {"device": "cpu", "gradient_accumulation_steps": 2}
+@pytest.mark.timeout(1500)
+@pytest.mark.parametrize("device", ["cpu", pytest.param("cuda", marks=pytest.mark.gpu)])
+def test_phase_chain(work, device):
+    """device="cuda": the same chain through the native kernels (bf16), one process on one GPU."""
+    _DEVICE[0] = device
+    d = work / device
+    d.mkdir(exist_ok=True)
+    for f in ("sft.jsonl", "pref.jsonl", "prompts.jsonl"):
+        (d / f).write_text((work / f).read_text())
+    hw = {"device": device, "gradient_accumulation_steps": 2}
     # ---- SFT (cosine schedule, eval split, prompt masking)
     sft_cfg = _write(d / "sft.yaml", {
         "seed": 1, "model": {"model_name_or_path": "tiny-llama", "max_seq_length": 64},
@@ -68,7 +79,7 @@ def test_phase_chain(work):
         "seed": 2, "model": {"base_model_name_or_path": str(latest), "pooling": "last_token", "dropout": 0.1, "max_seq_length": 48},
         "data": {"source": "local", "train_path": str(d / "pref.jsonl"), "eval_path": str(d / "pref.jsonl"), "num_workers": 0},
         "optimization": {"micro_batch_size": 2, "learning_rate": 1e-3, "max_train_steps": 2},
-        "logging": _log(d, "reward"), "hardware": {"device": "cpu"}})
+        "logging": _log(d, "reward"), "hardware": {"device": device}})
     out = _run("dla_b200.cli.train_reward", "--config", rw_cfg)
     assert "Reward model training complete" in out
     assert (d / "ckpt" / "reward" / "latest" / "pytorch_model.bin").exists()
@@ -78,7 +89,7 @@ def test_phase_chain(work):
                              "max_seq_length": 48},
         "data": {"source": "local", "preference_path": str(d / "pref.jsonl"), "num_workers": 0},
         "optimization": {"micro_batch_size": 2, "learning_rate": 1e-4, "max_train_steps": 2},
-        "logging": _log(d, "dpo"), "hardware": {"device": "cpu"}})
+        "logging": _log(d, "dpo"), "hardware": {"device": device}})
     out = _run("dla_b200.cli.train_dpo", "--config", dpo_cfg, "--overlay", str(ROOT / "config/ablations/high_beta_dpo.yaml"),
                "--override", "optimization.max_train_steps=2")
     assert "DPO training complete" in out
@@ -94,7 +105,7 @@ def test_phase_chain(work):
     base = {"seed": 4, "model": {"student_model_name_or_path": "tiny-llama", "max_seq_length": 48},
             "data": {"teacher_samples_path": str(roll), "num_workers": 0},
             "optimization": {"micro_batch_size": 2, "learning_rate": 1e-3, "max_train_steps": 2, "temperature": 2.0},
-            "logging": _log(d, "distill"), "hardware": {"device": "cpu"}}
+            "logging": _log(d, "distill"), "hardware": {"device": device}}
     out = _run("dla_b200.cli.train_distill", "--config", _write(d / "distill_ce.yaml", {**base, "distill": {"use_kl": False}}))
     assert "Distillation complete" in out
     kl = {**base, "distill": {"use_kl": True, "on_policy": True,
@@ -108,7 +119,7 @@ def test_phase_chain(work):
                   "generation_params": {"max_new_tokens": 5, "temperature": 0.7, "top_p": 0.9, "do_sample": True}},
           "sampling": {"source": "local", "prompt_path": str(d / "prompts.jsonl")},
           "logging": {"output_dir": str(d / "ckpt" / "rlhf"), "log_dir": str(d / "logs" / "rlhf"), "log_every_steps": 1},
-          "hardware": {"device": "cpu"}}
+          "hardware": {"device": device}}
     out = _run("dla_b200.cli.train_rlhf", "--config", _write(d / "rlhf.yaml", rl))
     assert "RLHF PPO loop complete" in out
     m = [json.loads(l) for l in (d / "logs" / "rlhf" / "metrics.jsonl").read_text().splitlines()]
