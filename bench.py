@@ -113,7 +113,7 @@ def main() -> None:
     if world != args.gpus and ctx.is_main:
         print(f"[bench] note: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
     dev = ctx.device
-    K, Wm, T, MB = args.steps, max(args.warmup, 0), args.seq_len, args.micro_batch
+    K, Wm, T, MB = args.steps, max(args.warmup, 3), args.seq_len, args.micro_batch      # never fewer than 3 warm-up steps
 
     note = None
     if args.impl == "reference":
