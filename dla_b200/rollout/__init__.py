@@ -246,6 +246,10 @@ class Generator:
         pad = eos if pad_token_id is None else pad_token_id
         plen = attention_mask.sum(1).to(torch.int32)
         max_len = Tp + max_new_tokens
+        if dev.type == "cuda":
+            # KV buffers (and the captured decode graph keyed by them) come in 64-position buckets, so rollouts whose
+            # prompt lengths differ a little share one session; rows still stop after max_new_tokens
+            max_len = (max_len + 63) // 64 * 64
         if cfg.arch == "gpt2":
             max_len = min(max_len, cfg.max_position_embeddings)
         dtype = self.p.acquire("embed")["tok_emb"].dtype
