@@ -124,6 +124,7 @@ struct Params {
   int c_fp32, accumulate;
   int store_mode;     // 0 = TMA store / reduce-add through staged smem, 1 = direct st.global from the TMEM layout
   int num_m_tiles, num_n_tiles;
+  int k_splits;       // > 1: every output tile is computed by k_splits CTAs over disjoint K ranges and reduce-added (C pre-zeroed)
   // log-prob epilogue
   const int64_t* labels;
   float2* partials;   // [num_n_tiles, M] (max, sumexp)
@@ -246,7 +247,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = (p.K + BK - 1) / BK;
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int out_tiles = p.num_m_tiles * p.num_n_tiles;
+  // split-K (small-M problems: too few output tiles to fill the machine): work item w = (K slice w / out_tiles,
+  // output tile w % out_tiles); slices of one tile land in C through the reduce-add epilogue
+  const int k_splits = p.k_splits > 1 ? p.k_splits : 1;
+  const int kb_per = (num_kb + k_splits - 1) / k_splits;
+  const int num_tiles = out_tiles * k_splits;
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmA);
@@ -285,10 +291,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           } while (seen != p.ag_epoch);
           asm volatile("fence.proxy.async;" ::: "memory");
         } else {
-          tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+          tile_coords(t % out_tiles, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
         }
         const int m0 = m_blk * BM, n0 = n_blk * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = (t / out_tiles) * kb_per, kb1 = min(num_kb, kb0 + kb_per);
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
@@ -323,7 +330,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const int kb0 = (t / out_tiles) * kb_per, kb1 = min(num_kb, kb0 + kb_per);
+        for (int kb = kb0; kb < kb1; ++kb) {
           tc::mbar_wait(&full_bar[stage], phase);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(smem + stage * STAGE_BYTES);
@@ -336,10 +344,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
                                      : tc::make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t db = kBMN ? tc::make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024)
                                      : tc::make_smem_desc(sb + k * 32, 16, 1024);
-            tc::umma_bf16<1>(tmem_d, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            tc::umma_bf16<1>(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           tc::umma_commit(&empty_bar[stage]);       // smem slot reusable once these MMAs retire
-          if (kb == num_kb - 1) tc::umma_commit(&tfull_bar[acc]);
+          if (kb == kb1 - 1) tc::umma_commit(&tfull_bar[acc]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -351,7 +359,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     for (int t = cta; t < num_tiles; t += n_cta, ++it) {
       int m_blk, n_blk;
       if (n_copy > 0) tile_coords_ag(t, p.num_m_tiles, p.num_n_tiles, ag_first, m_blk, n_blk);
-      else tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+      else tile_coords(t % out_tiles, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       tc::mbar_wait(&tfull_bar[acc], acc_phase);
@@ -563,6 +571,7 @@ logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, co
 }
 
 static int g_variant = 0;
+static int g_split_k = 1;        // small-M split-K (dla_gemm_set_variant(3) turns it off for A/B runs)
 static int g_auto_2cta = 1;      // measured on B200: faster than the 1-CTA kernel for K <= 16K (profiles/kernels_r1.jsonl)
 
 template <bool kAMN, bool kBMN, int kEpi>
@@ -573,7 +582,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
     DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     attr_set = true;
   }
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int num_tiles = p.num_m_tiles * p.num_n_tiles * (p.k_splits > 1 ? p.k_splits : 1);
   int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
   if (p.ag_ncopy > 0) grid = kNumSMs;     // copy + compute CTAs must all be co-resident (1 CTA / SM)
   kern<<<grid, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);
@@ -605,6 +614,8 @@ using namespace dla::gemm;
 extern "C" {
 
 int dla_gemm_set_variant(int variant) {
+  if (variant == 3) { g_split_k = 0; return 0; }     // 3 / 4: split-K off / on, the kernel choice is untouched
+  if (variant == 4) { g_split_k = 1; return 0; }
   g_variant = variant;
   return 0;
 }
@@ -637,6 +648,23 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
     if (rc) return rc;
   }
   cudaStream_t s = (cudaStream_t)stream;
+  // split-K when the output has far fewer tiles than SMs and K is long enough to share (prefill / small-batch
+  // forward: M = 256 gives 32 tiles for a 4096-wide projection).  Slices meet in C through TMA reduce-add, so C is
+  // zero-filled first unless the caller accumulates anyway.
+  const int out_tiles = p.num_m_tiles * p.num_n_tiles, num_kb = (K + BK - 1) / BK;
+  if (g_split_k && tma_ok && out_tiles * 2 <= kNumSMs && num_kb >= 16) {
+    int splits = kNumSMs / out_tiles;
+    if (splits > 8) splits = 8;
+    if (splits > num_kb / 8) splits = num_kb / 8;
+    while (splits > 1 && (splits - 1) * ((num_kb + splits - 1) / splits) >= num_kb) --splits;   // no empty K slice (it would never signal its epilogue)
+    if (splits > 1) {
+      p.k_splits = splits;
+      if (!accumulate) {
+        DLA_CUDA(cudaMemset2DAsync(C, (size_t)ldc * esz, 0, (size_t)N * esz, (size_t)M, s));
+        p.accumulate = 1;
+      }
+    }
+  }
   if (!a_mn_major && !b_mn_major) return launch<false, false, kStore>(tmA, tmB, tmC, p, s);
   if (!a_mn_major && b_mn_major) return launch<false, true, kStore>(tmA, tmB, tmC, p, s);
   if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, tmC, p, s);

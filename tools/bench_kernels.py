@@ -77,6 +77,22 @@ def main():
             N.call("dla_gemm_set_variant", 0)
             out.append(rec)
             print(json.dumps(rec), flush=True)
+    if "smallm" in which:
+        for M in (128, 256, 512, 1024):
+            for Nn, K, tag in [(6144, 4096, "qkv"), (4096, 4096, "wo"), (28672, 4096, "gate_up"), (4096, 14336, "down")]:
+                a, b = rnd(M, K), rnd(Nn, K)
+                c = torch.empty(M, Nn, device=DEV, dtype=torch.bfloat16)
+                flops = 2.0 * M * Nn * K
+                N.call("dla_gemm_set_variant", 4)
+                t_on = timeit(lambda: F.gemm(a, b, out=c))
+                N.call("dla_gemm_set_variant", 3)
+                t_off = timeit(lambda: F.gemm(a, b, out=c))
+                N.call("dla_gemm_set_variant", 4)
+                t_lib = timeit(lambda: torch.matmul(a, b.t(), out=c))
+                rec = {"kernel": "gemm_small_m", "tag": tag, "M": M, "N": Nn, "K": K, "ms_splitk": t_on, "ms_no_split": t_off, "cublas_ms": t_lib,
+                       "tflops": flops / t_on / 1e9, "weight_gbs": 2.0 * Nn * K / t_on / 1e6}
+                out.append(rec)
+                print(json.dumps(rec), flush=True)
     if "skinny" in which:
         for M in (1, 8, 16):
             for Nn, K, tag in [(6144, 4096, "qkv"), (4096, 4096, "wo"), (28672, 4096, "gate_up"), (4096, 14336, "down"), (128256, 4096, "lm_head")]:
