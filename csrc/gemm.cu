@@ -606,6 +606,7 @@ static int build_maps(CUtensorMap* tmA, CUtensorMap* tmB, const void* A, const v
 namespace dla {
 int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
                    int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream);
+void gemm2_set_tail_split(int on);
 }
 
 using namespace dla;
@@ -614,8 +615,10 @@ using namespace dla::gemm;
 extern "C" {
 
 int dla_gemm_set_variant(int variant) {
-  if (variant == 3) { g_split_k = 0; return 0; }     // 3 / 4: split-K off / on, the kernel choice is untouched
+  if (variant == 3) { g_split_k = 0; return 0; }     // 3 / 4: small-M split-K off / on, the kernel choice is untouched
   if (variant == 4) { g_split_k = 1; return 0; }
+  if (variant == 5) { gemm2_set_tail_split(0); return 0; }   // 5 / 6: last-wave K split of the 2-CTA kernel off / on
+  if (variant == 6) { gemm2_set_tail_split(1); return 0; }
   g_variant = variant;
   return 0;
 }

@@ -36,7 +36,37 @@ struct Params {
   int M, N, K;
   int c_fp32, accumulate;
   int num_m_tiles, num_n_tiles;      // in 256 x 256 cluster tiles
+  // wave-quantisation fix: the last (partial) wave of `tail_tiles` tiles is computed as tail_tiles x tail_splits work
+  // items over disjoint K slices, one per cluster, combined by TMA reduce-add (those tiles are zero-filled by
+  // zero_tail_kernel first unless the caller accumulates).  tail_splits <= 1: off.
+  int tail_tiles, tail_splits;
 };
+
+// work item w -> (tile, K-block range).  Items below `full` are whole tiles; the rest are K slices of the tail tiles,
+// laid out slice-major so that the slices of one tile sit on different clusters of the same (last) wave.
+struct Work {
+  int tile, kb0, kb1;
+  bool split;
+};
+__device__ __forceinline__ Work work_item(int w, const Params& p, int num_tiles, int num_kb) {
+  Work x;
+  const int full = num_tiles - (p.tail_splits > 1 ? p.tail_tiles : 0);
+  if (w < full) {
+    x.tile = w;
+    x.kb0 = 0;
+    x.kb1 = num_kb;
+    x.split = false;
+  } else {
+    const int i = w - full;
+    const int slice = i / p.tail_tiles;
+    const int per = (num_kb + p.tail_splits - 1) / p.tail_splits;
+    x.tile = full + i % p.tail_tiles;
+    x.kb0 = slice * per;
+    x.kb1 = min(num_kb, x.kb0 + per);
+    x.split = true;
+  }
+  return x;
+}
 
 __device__ __forceinline__ uint32_t pack2(uint32_t a, uint32_t b) {
   bf162 v = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b));
@@ -87,6 +117,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   const int cluster_id = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
   const int num_kb = (p.K + BK - 1) / BK;
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int num_items = num_tiles + (p.tail_splits > 1 ? p.tail_tiles * (p.tail_splits - 1) : 0);
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmA);
@@ -114,11 +145,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = cluster_id; t < num_tiles; t += n_clusters) {
+      for (int w = cluster_id; w < num_items; w += n_clusters) {
+        const Work wk = work_item(w, p, num_tiles, num_kb);
         int m_blk, n_blk;
-        tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+        tile_coords(wk.tile, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
         const int m0 = m_blk * 256 + (int)cta * BM, n0 = n_blk * BN + (int)cta * BNH;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = wk.kb0; kb < wk.kb1; ++kb) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
           uint8_t* sb = sa + A_BYTES;
@@ -148,13 +180,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
-      for (int t = cluster_id; t < num_tiles; t += n_clusters, ++it) {
+      for (int w = cluster_id; w < num_items; w += n_clusters, ++it) {
+        const Work wk = work_item(w, p, num_tiles, num_kb);
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1;
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc::tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = wk.kb0; kb < wk.kb1; ++kb) {
           tc::mbar_wait(&full_bar[stage], phase);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(smem + stage * STAGE_BYTES);
@@ -163,10 +196,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t da = kAMN ? tc::make_smem_desc(sa + k * 2048, 64 * BK * 2, 1024) : tc::make_smem_desc(sa + k * 32, 16, 1024);
             const uint64_t db = kBMN ? tc::make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024) : tc::make_smem_desc(sb + k * 32, 16, 1024);
-            tc::umma_bf16<2>(tmem_d, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            tc::umma_bf16<2>(tmem_d, da, db, idesc, (kb > wk.kb0 || k > 0) ? 1u : 0u);
           }
           tc::umma_commit_2sm(&empty_bar[stage], 0b11);                      // both CTAs' smem slots are reusable
-          if (kb == num_kb - 1) tc::umma_commit_2sm(&tfull_bar[acc], 0b11);  // both CTAs' accumulator halves are ready
+          if (kb == wk.kb1 - 1) tc::umma_commit_2sm(&tfull_bar[acc], 0b11);  // both CTAs' accumulator halves are ready
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -177,9 +210,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const uint32_t tempty_leader0 = mapa_u32(tc::smem_u32(&tempty_bar[0]), 0);
     const uint32_t tempty_leader1 = mapa_u32(tc::smem_u32(&tempty_bar[1]), 0);
     int it = 0;
-    for (int t = cluster_id; t < num_tiles; t += n_clusters, ++it) {
+    for (int w = cluster_id; w < num_items; w += n_clusters, ++it) {
+      const Work wk = work_item(w, p, num_tiles, num_kb);
+      const bool add = p.accumulate != 0 || wk.split;       // K slices of a tail tile meet in C by reduce-add
       int m_blk, n_blk;
-      tile_coords(t, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
+      tile_coords(wk.tile, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       tc::mbar_wait(&tfull_bar[acc], acc_phase);
@@ -223,7 +258,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         if (lane == 0) {
           const int c0 = col_base + gi * gc;
           if (c0 < p.N && r0 < p.M) {
-            if (p.accumulate) tc::tma_reduce_add_2d(&tmC, buf, c0, r0);
+            if (add) tc::tma_reduce_add_2d(&tmC, buf, c0, r0);
             else tc::tma_store_2d(&tmC, buf, c0, r0);
           }
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
@@ -246,6 +281,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
   }
 }
 
+// zero-fills the tail tiles (block = one 128-row half of one tile) ahead of their reduce-add slices
+__global__ void __launch_bounds__(256)
+zero_tail_kernel(uint8_t* __restrict__ C, int64_t ld_bytes, int esz, int M, int N, int num_m, int num_n, int first_tile) {
+  int m_blk, n_blk;
+  tile_coords(first_tile + (int)(blockIdx.x >> 1), num_m, num_n, m_blk, n_blk);
+  const int r0 = m_blk * 256 + (int)(blockIdx.x & 1) * 128, c0 = n_blk * BN;
+  const int rows = min(128, M - r0), cols = min(BN, N - c0);
+  if (rows <= 0 || cols <= 0) return;
+  const int vec_per_row = cols * esz / 16;                 // row pitch and tile origin are 16-byte aligned (TMA contract)
+  const int tail_bytes = cols * esz - vec_per_row * 16;
+  for (int i = threadIdx.x; i < rows * vec_per_row; i += blockDim.x) {
+    const int r = i / vec_per_row, v = i - r * vec_per_row;
+    *reinterpret_cast<uint4*>(C + (int64_t)(r0 + r) * ld_bytes + (int64_t)c0 * esz + v * 16) = make_uint4(0, 0, 0, 0);
+  }
+  if (tail_bytes > 0)
+    for (int i = threadIdx.x; i < rows * tail_bytes; i += blockDim.x) {
+      const int r = i / tail_bytes, b = i - r * tail_bytes;
+      C[(int64_t)(r0 + r) * ld_bytes + (int64_t)c0 * esz + vec_per_row * 16 + b] = 0;
+    }
+}
+
 template <bool kAMN, bool kBMN>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
   auto kern = gemm2_kernel<kAMN, kBMN>;
@@ -261,6 +317,9 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
 }
 
 }  // namespace gemm2
+
+static int g_tail_split = 1;
+void gemm2_set_tail_split(int on) { g_tail_split = on; }
 
 // called from dla_gemm_bf16 (gemm.cu)
 int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
@@ -282,6 +341,23 @@ int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, i
   p.M = M; p.N = N; p.K = K; p.c_fp32 = c_fp32; p.accumulate = accumulate;
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
+  // last partial wave: if it fills at most half of the clusters, split its tiles along K so the wave is full
+  const int T = p.num_m_tiles * p.num_n_tiles, Cn = kNumSMs / 2, num_kb = (K + BK - 1) / BK;
+  const int R = T > Cn ? T % Cn : 0;
+  if (g_tail_split && R > 0 && 2 * R <= Cn && num_kb >= 16) {
+    int sp = Cn / R;
+    if (sp > 8) sp = 8;
+    if (sp > num_kb / 8) sp = num_kb / 8;
+    while (sp > 1 && (sp - 1) * ((num_kb + sp - 1) / sp) >= num_kb) --sp;       // no empty K slice
+    if (sp > 1) {
+      p.tail_tiles = R;
+      p.tail_splits = sp;
+      if (!accumulate) {
+        zero_tail_kernel<<<2 * R, 256, 0, stream>>>(reinterpret_cast<uint8_t*>(C), ldc * esz, esz, M, N, p.num_m_tiles, p.num_n_tiles, T - R);
+        if (int zrc = check_launch("gemm2.zero_tail")) return zrc;
+      }
+    }
+  }
   if (!a_mn && !b_mn) return launch<false, false>(tmA, tmB, tmC, p, stream);
   if (!a_mn && b_mn) return launch<false, true>(tmA, tmB, tmC, p, stream);
   if (a_mn && !b_mn) return launch<true, false>(tmA, tmB, tmC, p, stream);

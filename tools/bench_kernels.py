@@ -60,9 +60,12 @@ def main():
             t_own = timeit(lambda: F.gemm(a, b, out=c))
             N.call("dla_gemm_set_variant", 2)
             t_2cta = timeit(lambda: F.gemm(a, b, out=c))
+            N.call("dla_gemm_set_variant", 5)            # last-wave K split off
+            t_2cta_notail = timeit(lambda: F.gemm(a, b, out=c))
+            N.call("dla_gemm_set_variant", 6)
             N.call("dla_gemm_set_variant", 0)
             t_lib = timeit(lambda: torch.matmul(a, b.t(), out=c))
-            rec = {"kernel": "gemm_nt", "tag": tag, "M": M, "N": Nn, "K": K, "ms": t_own, "tflops": flops / t_own / 1e9, "tflops_2cta": flops / t_2cta / 1e9,
+            rec = {"kernel": "gemm_nt", "tag": tag, "M": M, "N": Nn, "K": K, "ms": t_own, "tflops": flops / t_own / 1e9, "tflops_2cta": flops / t_2cta / 1e9, "tflops_2cta_no_tail_split": flops / t_2cta_notail / 1e9,
                    "cublas_ms": t_lib, "cublas_tflops": flops / t_lib / 1e9,
                    "frac_of_measured_peak": flops / t_own / 1e9 / PK["bf16_tflops"]}
             # dgrad (B mn-major) and wgrad (both mn-major) of the same Linear
@@ -74,6 +77,10 @@ def main():
             N.call("dla_gemm_set_variant", 2)
             rec["dgrad_tflops_2cta"] = flops / timeit(lambda: F.gemm(dy, b, b_mn=True, out=dx)) / 1e9
             rec["wgrad_tflops_2cta"] = flops / timeit(lambda: F.gemm(dy, a, a_mn=True, b_mn=True, out=dw)) / 1e9
+            N.call("dla_gemm_set_variant", 5)
+            rec["dgrad_tflops_2cta_no_tail_split"] = flops / timeit(lambda: F.gemm(dy, b, b_mn=True, out=dx)) / 1e9
+            rec["wgrad_tflops_2cta_no_tail_split"] = flops / timeit(lambda: F.gemm(dy, a, a_mn=True, b_mn=True, out=dw)) / 1e9
+            N.call("dla_gemm_set_variant", 6)
             N.call("dla_gemm_set_variant", 0)
             out.append(rec)
             print(json.dumps(rec), flush=True)
