@@ -344,7 +344,9 @@ int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, i
   // last partial wave: if it fills at most half of the clusters, split its tiles along K so the wave is full
   const int T = p.num_m_tiles * p.num_n_tiles, Cn = kNumSMs / 2, num_kb = (K + BK - 1) / BK;
   const int R = T > Cn ? T % Cn : 0;
-  if (g_tail_split && R > 0 && 2 * R <= Cn && num_kb >= 16) {
+  // Only where the slices add into storage that accumulates anyway (gradient buckets, fp32 outputs): a bf16 activation
+  // tile keeps its single fp32-accumulated rounding, identical to the unsplit kernel.
+  if (g_tail_split && (accumulate || c_fp32) && R > 0 && 2 * R <= Cn && num_kb >= 16) {
     int sp = Cn / R;
     if (sp > 8) sp = 8;
     if (sp > num_kb / 8) sp = num_kb / 8;
