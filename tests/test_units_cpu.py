@@ -201,3 +201,25 @@ def test_scalar_head_reference_matches_dropout_linear_pooling():
     # the functional entry point routes CPU tensors to the same restatement
     assert torch.equal(F.scalar_head(hid, mask, lin.weight, lin.bias, keep, "last_token"),
                        R.scalar_head(hid, mask, lin.weight, lin.bias, keep, "last_token"))
+
+
+def test_gradient_slot_protocol():
+    """ops.functional._slot_gemm / _slot_add: a fresh slot is overwritten by the first wgrad GEMM and zero-filled before any
+    accumulating writer; the engine only marks slots fresh that have been fed by a GEMM (``_ow``)."""
+    import torch
+
+    from dla_b200.ops import functional as F
+
+    w = torch.zeros(4, 8)
+    slot = torch.full((4, 8), 7.0)
+    w._grad_slot = slot
+    got, acc = F._slot_gemm(w)
+    assert got is slot and acc is True and slot._ow is True          # never marked fresh: accumulate as always
+    slot._fresh = True                                               # what Engine._zero_unit does instead of a memset
+    got, acc = F._slot_gemm(w)
+    assert acc is False and slot._fresh is False                     # first GEMM of the step overwrites ...
+    assert F._slot_gemm(w)[1] is True                                # ... later ones accumulate
+    slot._fresh = True
+    assert F._slot_add(w) is slot and float(slot.abs().sum()) == 0.0 and slot._fresh is False   # adders see real zeros
+    assert F._slot_add(torch.zeros(2)) is None and F._slot_add(None) is None
+    assert F._slot_gemm(torch.zeros(2)) == (None, False)
