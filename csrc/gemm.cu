@@ -12,6 +12,7 @@
 // Reference path replaced: nn.Linear -> cuBLASLt (R/src/training/train_dpo.py:32) and
 // log_softmax + gather over the vocab (R/src/training/train_dpo.py:33-38).
 #include <math.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <unordered_map>
@@ -572,7 +573,7 @@ logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, co
 
 static int g_variant = 0;
 static int g_split_k = 1;        // small-M split-K (dla_gemm_set_variant(3) turns it off for A/B runs)
-static int g_auto_2cta = 1;      // measured on B200: faster than the 1-CTA kernel for K <= 16K (profiles/kernels_r1.jsonl)
+static int g_auto_2cta = 1;      // measured on B200 (profiles/kernels_r1_2cta.jsonl, tools/gpu_ab_k.sh)
 
 template <bool kAMN, bool kBMN, int kEpi>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
@@ -642,7 +643,12 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   p.store_mode = tma_ok ? 0 : 1;
   // 2-CTA (cta_group::2) kernel: 256x256 cluster tiles; worth it once there is about a wave of them
   const int64_t tiles2 = (int64_t)((M + 255) / 256) * ((N + 255) / 256);
-  if (tma_ok && (g_variant == 2 || (g_variant == 0 && g_auto_2cta && tiles2 >= kNumSMs / 2 && M >= 256 && K <= 16384)))
+  static const int max_k_2cta = [] {
+    const char* e = getenv("DLA_GEMM_2CTA_MAX_K");       // A/B knob.  In isolation the 1-CTA kernel wins above K = 16K, inside the
+                                                         // power-capped step the 2-CTA kernel (less shared-memory traffic per flop) does
+    return e != nullptr ? atoi(e) : 32768;
+  }();
+  if (tma_ok && (g_variant == 2 || (g_variant == 0 && g_auto_2cta && tiles2 >= kNumSMs / 2 && M >= 256 && K <= max_k_2cta)))
     return gemm2_dispatch(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, c_fp32, accumulate, (cudaStream_t)stream);
   CUtensorMap tmC{};
   if (tma_ok) {
