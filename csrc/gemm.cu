@@ -573,7 +573,7 @@ logprob_grad_kernel(bf16* __restrict__ logits, const float* __restrict__ lse, co
 
 static int g_variant = 0;
 static int g_split_k = 1;        // small-M split-K (dla_gemm_set_variant(3) turns it off for A/B runs)
-static int g_auto_2cta = 1;      // measured on B200 (profiles/kernels_r1_2cta.jsonl, tools/gpu_ab_k.sh)
+static int g_auto_2cta = 1;      // measured on B200 (profiles/kernels_r1_2cta.jsonl, tools/gpu/ab_k.sh)
 
 template <bool kAMN, bool kBMN, int kEpi>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {

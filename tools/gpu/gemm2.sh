@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-FILE=tests/test_gpu_kernels.py TESTS="test_gemm_2cta_variant" TMO=200 bash tools/gpu_kernel_sweep.sh
+FILE=tests/test_gpu_kernels.py TESTS="test_gemm_2cta_variant" TMO=200 bash tools/gpu/kernel_sweep.sh
 grep -E "^E  |Error|rror" gpurun_out/test_gemm_2cta_variant.log | head -8
 timeout 400 python tools/bench_kernels.py gemm 2>&1 | tail -8 | python -c "
 import sys,json

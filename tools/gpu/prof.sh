@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-FILE=tests/test_gpu_kernels.py TESTS="test_top_p_sampler_kernel" TMO=300 bash tools/gpu_kernel_sweep.sh
+FILE=tests/test_gpu_kernels.py TESTS="test_top_p_sampler_kernel" TMO=300 bash tools/gpu/kernel_sweep.sh
 grep -E "^E  " gpurun_out/test_top_p_sampler_kernel.log | head -5
 for w in gemm attn_fwd attn_bwd; do
   python tools/profile_target.py $w > gpurun_out/plain_$w.log 2>&1 && \
