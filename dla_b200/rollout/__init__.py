@@ -252,6 +252,11 @@ class Generator:
             max_len = (max_len + 63) // 64 * 64
         if cfg.arch == "gpt2":
             max_len = min(max_len, cfg.max_position_embeddings)
+        elif Tp + max_new_tokens > cfg.max_position_embeddings:
+            raise ValueError(f"prompt ({Tp}) + max_new_tokens ({max_new_tokens}) exceeds the model's {cfg.max_position_embeddings} "
+                             f"positions (the RoPE tables end there)")
+        else:
+            max_len = min(max_len, cfg.max_position_embeddings)
         dtype = self.p.acquire("embed")["tok_emb"].dtype
         temp = float(temperature) if do_sample else 0.0
         seed = seed if seed is not None else int(torch.randint(0, 2**31 - 1, (1,)).item())
