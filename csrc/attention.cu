@@ -684,6 +684,7 @@ int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
   p.o = (bf16*)o; p.o_sb = o_sb; p.o_st = o_st; p.o_sh = o_sh; p.lse = lse;
   dim3 grid((T + BQ - 1) / BQ, Hq, B);
   cudaStream_t s = (cudaStream_t)stream;
+  if (g_fwd_variant == 3) return attn_fwd3_dispatch(tmQ, tmK, tmV, p, s);     // early-S ping-pong kernel (attn_fwd3.cu)
   if (g_fwd_variant != 1) return attn_fwd2_dispatch(tmQ, tmK, tmV, p, s);     // ping-pong kernel (attn_fwd2.cu)
   if (D == 128) {
     constexpr int smem = 128 * 128 * 2 + 2 * 2 * 128 * 128 * 2 + 128 * 128 * 2 + 1024 + 4096;

@@ -49,6 +49,8 @@ inline int make_qkv_map(CUtensorMap* m, const void* base, int B, int T, int H, i
 
 // attn_fwd2.cu
 int attn_fwd2_dispatch(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t s);
+// attn_fwd3.cu
+int attn_fwd3_dispatch(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t s);
 
 }  // namespace attn
 }  // namespace dla

@@ -169,7 +169,8 @@ int dla_lmhead_logprob_noalloc_max_vocab(void);
  * strides (batch, token, head); D == 128 or 64.  seqlens (nullable int32 [B]) masks right padding.
  * lse: fp32 [B,Hq,T]. */
 /* Forward kernel choice: 0 = auto (two-query-tile ping-pong kernel, csrc/attn_fwd2.cu), 1 = first-generation
- * one-tile kernel (csrc/attention.cu), 2 = ping-pong.  Process-wide; for benchmarks and A/B tests. */
+ * one-tile kernel (csrc/attention.cu), 2 = ping-pong, 3 = ping-pong with early S release / P through shared memory
+ * (csrc/attn_fwd3.cu; measured slower, experimental).  Process-wide; for benchmarks and A/B tests. */
 int dla_attn_set_fwd_variant(int v);
 int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse,
                  int B, int T, int Hq, int Hk, int D,

@@ -310,6 +310,29 @@ def test_attention_fwd_bwd(native_lib, B, T, Hq, Hk, D, ragged):
     assert torch.equal(x2.grad, x.grad)
 
 
+@pytest.mark.parametrize("B,T,Hq,Hk,D,ragged", ATTN_CASES)
+def test_attention_fwd_early_s_variant(native_lib, B, T, Hq, Hk, D, ragged):
+    """csrc/attn_fwd3.cu (S released early, P through shared memory, event-driven MMA warp) against the fp32 reference."""
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(12)
+    qkv = _rand(B, T, Hq + 2 * Hk, D)
+    seqlens = None
+    if ragged:
+        seqlens = torch.randint(max(1, T // 3), T + 1, (B,), device=DEV, dtype=torch.int32)
+    q, k, v = qkv[:, :, :Hq], qkv[:, :, Hq:Hq + Hk], qkv[:, :, Hq + Hk:]
+    N.call("dla_attn_set_fwd_variant", 3)
+    try:
+        o = F.attention(q, k, v, seqlens=seqlens, causal=True)
+        torch.cuda.synchronize()
+    finally:
+        N.call("dla_attn_set_fwd_variant", 0)
+    oref = R.attention(q.float(), k.float(), v.float(), causal=True, seqlens=seqlens)
+    _close(o, oref, rtol=2e-2, atol=2e-2, what="attn fwd3")
+    o2 = F.attention(q, k, v, seqlens=seqlens, causal=True)
+    _close(o, o2, rtol=1e-2, atol=1e-2, what="fwd3 vs fwd2")
+
+
 def test_attention_separate_tensors(native_lib):
     torch.manual_seed(12)
     B, T, Hq, Hk, D = 2, 256, 4, 2, 128

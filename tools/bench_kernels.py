@@ -120,6 +120,8 @@ def main():
             fl = 4.0 * B * Hq * T * T * D / 2
             N.call("dla_attn_set_fwd_variant", 1)
             t_f1 = timeit(lambda: F.attention(q.detach(), k.detach(), v.detach()))
+            N.call("dla_attn_set_fwd_variant", 3)
+            t_f3 = timeit(lambda: F.attention(q.detach(), k.detach(), v.detach()))
             N.call("dla_attn_set_fwd_variant", 0)
             t_f = timeit(lambda: F.attention(q.detach(), k.detach(), v.detach()))
             o = F.attention(q, k, v)
@@ -127,7 +129,7 @@ def main():
             t_b = timeit(lambda: torch.autograd.grad(o, qkv, g, retain_graph=True))
             qs, ks, vs = (t.detach().transpose(1, 2).contiguous() for t in (q, k, v))
             t_sdpa = timeit(lambda: torch.nn.functional.scaled_dot_product_attention(qs, ks, vs, is_causal=True, enable_gqa=True))
-            rec = {"kernel": "attention", "B": B, "T": T, "Hq": Hq, "Hk": Hk, "D": D, "fwd_ms": t_f, "fwd_tflops": fl / t_f / 1e9, "fwd_gen1_ms": t_f1,
+            rec = {"kernel": "attention", "B": B, "T": T, "Hq": Hq, "Hk": Hk, "D": D, "fwd_ms": t_f, "fwd_tflops": fl / t_f / 1e9, "fwd_gen1_ms": t_f1, "fwd_gen3_ms": t_f3,
                    "bwd_ms": t_b, "bwd_tflops": 2.5 * fl / t_b / 1e9, "sdpa_fwd_ms": t_sdpa, "sdpa_fwd_tflops": fl / t_sdpa / 1e9}
             out.append(rec)
             print(json.dumps(rec), flush=True)
