@@ -1,8 +1,13 @@
 #!/usr/bin/env bash
-# evaluation: alignment proxies, then the prefill latency grid (single process, like the reference)
+# Evaluation phase.  Two single-process passes over the same YAML: (1) alignment proxies per model x benchmark
+# (results.json + summary.md), (2) the prefill latency grid (latency.json; one CUDA graph per batch x sequence shape).
+# usage: scripts/launch_eval.sh [config/eval_config.yaml]
 set -euo pipefail
-cd "$(dirname "$0")/.."
-CONFIG=${1:-config/eval_config.yaml}
+repo_root="$(cd "$(dirname "${BASH_SOURCE[0]}")/.." && pwd)"
+cd "$repo_root"
+cfg="${1:-config/eval_config.yaml}"
+
 export TOKENIZERS_PARALLELISM=false
-python -m dla_b200.cli.eval_alignment --config "$CONFIG"
-python -m dla_b200.cli.eval_latency --config "$CONFIG"
+for module in eval_alignment eval_latency; do
+  python -m "dla_b200.cli.${module}" --config "$cfg"
+done
