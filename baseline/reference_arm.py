@@ -128,3 +128,86 @@ class ReferenceDPO:
         self.opt.step()
         self.opt.zero_grad()
         return loss.detach()
+
+
+def synthetic_preference_batch(batch: int, seq_len: int, vocab_size: int, seed: int = 0,
+                               pin: bool = False) -> Dict[str, Dict[str, torch.Tensor]]:
+    """Same shapes, seeds and value range as the own arm's generator (``dla_b200/data/synthetic.py``), restated
+    with plain torch so this process never imports the framework under test."""
+    g = torch.Generator().manual_seed(seed)
+    out: Dict[str, Dict[str, torch.Tensor]] = {}
+    for side in ("chosen", "rejected"):
+        ids = torch.randint(4, vocab_size, (batch, seq_len), generator=g, dtype=torch.long)
+        mask = torch.ones(batch, seq_len, dtype=torch.long)
+        if pin and torch.cuda.is_available():
+            ids, mask = ids.pin_memory(), mask.pin_memory()
+        out[side] = {"input_ids": ids, "attention_mask": mask}
+    return out
+
+
+class ReferenceArm:
+    """Everything ``bench.py --impl reference`` needs, on stock torch only: rendezvous, barrier, max over ranks,
+    data, and the step.  ``bench.py`` drives it through the same timing loop as the own arm."""
+
+    impl = "reference"
+
+    def __init__(self, args: Any) -> None:
+        import datetime
+
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        local = int(os.environ.get("LOCAL_RANK", str(self.rank)))
+        self.device = torch.device("cuda", local % max(torch.cuda.device_count(), 1))
+        torch.cuda.set_device(self.device)
+        if self.world > 1 and not dist.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29500")
+            dist.init_process_group("nccl", rank=self.rank, world_size=self.world, device_id=self.device,
+                                    timeout=datetime.timedelta(seconds=1800))
+        self.is_main = self.rank == 0
+        self.runner = ReferenceDPO(args.model, self.device, self.world, sharded=(args.sharding != "ddp"))
+        self.vocab = llama_hf_config(args.model).vocab_size
+        self.note = ("reference compute_logprobs/dpo_loss unmodified from baseline/_ref, HF LlamaForCausalLM + torch "
+                     "AdamW + FSDP2/NCCL; accelerate/deepspeed absent so its main() cannot run (see DESIGN.md)")
+
+    # -- plumbing --------------------------------------------------------------------------------
+    def barrier(self) -> None:
+        if self.world > 1:
+            dist.barrier(device_ids=[self.device.index])
+
+    def max_over_ranks(self, v: float) -> float:
+        if self.world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=self.device)
+        dist.all_reduce(t, dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def make_batch(self, mb: int, T: int, seed: int):
+        return synthetic_preference_batch(mb, T, self.vocab, seed=seed, pin=True)
+
+    # -- the step --------------------------------------------------------------------------------
+    def step(self, batch):
+        return self.runner.step(batch)
+
+    def after_warmup_step(self, i: int, tokens: int) -> None:
+        pass
+
+    def retry_after_oom(self) -> bool:
+        return False
+
+    def before_stop(self) -> None:
+        pass
+
+    def launches(self) -> int:
+        return 0        # none of this repo's kernels exist in this process; see ``native_so_in_process``
+
+    def describe(self) -> Dict[str, Any]:
+        return {"optimizer": "torch AdamW on bf16 params", "activation_checkpointing": True}
+
+    @staticmethod
+    def native_so_in_process() -> bool:
+        """True if this repo's kernel library got mapped into the process after all (it must not be)."""
+        try:
+            return "libdla_b200" in open("/proc/self/maps").read()
+        except OSError:
+            return False

@@ -223,3 +223,27 @@ def test_gradient_slot_protocol():
     assert F._slot_add(w) is slot and float(slot.abs().sum()) == 0.0 and slot._fresh is False   # adders see real zeros
     assert F._slot_add(torch.zeros(2)) is None and F._slot_add(None) is None
     assert F._slot_gemm(torch.zeros(2)) == (None, False)
+
+
+def test_reference_arm_never_imports_the_framework():
+    """``bench.py --impl reference`` must not pull this package (or its kernel library) into the process:
+    importing the arm module and generating a batch in a fresh interpreter leaves ``dla_b200`` unimported,
+    and the arm's batch equals the own arm's generator bit for bit (same seeds, same shapes)."""
+    import subprocess
+    import sys
+    from pathlib import Path
+
+    root = Path(__file__).resolve().parents[1]
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from baseline import reference_arm as ra\n"
+            "b = ra.synthetic_preference_batch(2, 16, 100, seed=5)\n"
+            "assert not any(m.split('.')[0] == 'dla_b200' for m in sys.modules), 'framework imported'\n"
+            "assert 'libdla_b200' not in open('/proc/self/maps').read()\n"
+            "print(b['chosen']['input_ids'].sum().item(), b['rejected']['input_ids'].sum().item())\n") % str(root)
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    from dla_b200.data.synthetic import synthetic_preference_batch
+
+    own = synthetic_preference_batch(2, 16, 100, seed=5)
+    a, b = (int(x) for x in out.stdout.split())
+    assert a == int(own["chosen"]["input_ids"].sum()) and b == int(own["rejected"]["input_ids"].sum())
