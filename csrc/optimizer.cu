@@ -50,15 +50,27 @@ __device__ __forceinline__ void store_moment8(void* base, int64_t o, const float
   }
 }
 
+// 16 bytes stored through the NVSwitch multicast address: lands in every rank's copy of the buffer
+__device__ __forceinline__ void multimem_st8(bf16* mc, const bf16x8& v) {
+  const uint4 u = *reinterpret_cast<const uint4*>(&v);
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(__uint_as_float(u.x)),
+               "f"(__uint_as_float(u.y)), "f"(__uint_as_float(u.z)), "f"(__uint_as_float(u.w)) : "memory");
+}
+
 // One thread = 8 consecutive elements: 16 B of grad, 3 x 32 B of fp32 state in, 3 x 32 B + 16 B out
-// (2 x 16 B each way for the moments when they are bf16).
-template <bool kGradF32, bool kMomBF16>
+// (2 x 16 B each way for the moments when they are bf16).  kMC: `param` is a MULTICAST address — the updated bf16
+// shard is written into every rank's resident parameters by the same store (the post-step all-gather disappears).
+// A clip coefficient of exactly 0 means "non-finite gradient norm": the whole update, weight decay included, is skipped
+// (g * 0 would still poison the moments with NaN).
+template <bool kGradF32, bool kMomBF16, bool kMC = false>
 __global__ void __launch_bounds__(256)
 adamw_kernel(float* __restrict__ master, void* __restrict__ m, void* __restrict__ v,
              const void* __restrict__ grad, bf16* __restrict__ param, int64_t n, float lr, float beta1,
              float beta2, float eps, float wd, float inv_bc1, float inv_sqrt_bc2,
              const float* __restrict__ grad_scale_dev, float prescale) {
-  const float gs = prescale * (grad_scale_dev != nullptr ? *grad_scale_dev : 1.f);
+  const float coef = grad_scale_dev != nullptr ? *grad_scale_dev : 1.f;
+  if (coef == 0.f) return;
+  const float gs = prescale * coef;
   const uint32_t step_seed = __float_as_uint(inv_sqrt_bc2) * 0x9E3779B9u;   // changes every optimizer step
   const int64_t nvec = n >> 3;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
@@ -86,10 +98,11 @@ adamw_kernel(float* __restrict__ master, void* __restrict__ m, void* __restrict_
     *reinterpret_cast<float4*>(master + o + 4) = *reinterpret_cast<float4*>(p + 4);
     store_moment8<kMomBF16>(m, o, mm, step_seed);
     store_moment8<kMomBF16>(v, o, vv, step_seed ^ 0xA5A5A5A5u);
-    if (param != nullptr) st8(param + o, pack8(p));
+    if (kMC) multimem_st8(param + o, pack8(p));
+    else if (param != nullptr) st8(param + o, pack8(p));
   }
-  // tail (n % 8) handled by the first threads of block 0
-  if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+  // tail (n % 8) handled by the first threads of block 0 (never taken with kMC: shards are multiples of 8)
+  if (!kMC && blockIdx.x == 0 && threadIdx.x < (n & 7)) {
     const int64_t o = (nvec << 3) + threadIdx.x;
     float gj = (kGradF32 ? ((const float*)grad)[o] : __bfloat162float(((const bf16*)grad)[o])) * gs;
     const float m0 = kMomBF16 ? __bfloat162float(((const bf16*)m)[o]) : ((const float*)m)[o];
@@ -201,6 +214,30 @@ int dla_adamw(float* master, void* m, void* v, const void* grad, void* param, in
   else DLA_ADAMW_LAUNCH(false, false);
 #undef DLA_ADAMW_LAUNCH
   return check_launch("adamw");
+}
+
+int dla_adamw_mc(float* master, void* m, void* v, const void* grad, void* mc_param, int64_t n, float lr, float beta1,
+                 float beta2, float eps, float weight_decay, float bias_c1, float bias_c2, const float* grad_scale_dev,
+                 float grad_prescale, int flags, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(bias_c1 > 0.f && bias_c2 > 0.f, DLA_E_BADARG, "adamw_mc: bias corrections must be > 0");
+  DLA_REQUIRE(mc_param != nullptr && n % 8 == 0 && (reinterpret_cast<uintptr_t>(mc_param) & 15) == 0, DLA_E_BADARG,
+              "adamw_mc: needs a 16-byte aligned multicast address and n %% 8 == 0");
+  if (n == 0) return 0;
+  int64_t blocks = ((n >> 3) + 255) / 256;
+  if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
+  const float inv_bc1 = 1.f / bias_c1, inv_sqrt_bc2 = 1.f / sqrtf(bias_c2);
+  const bool g32 = (flags & DLA_ADAMW_GRAD_FP32) != 0, mom16 = (flags & DLA_ADAMW_MOMENTS_BF16) != 0;
+  cudaStream_t st = (cudaStream_t)stream;
+#define DLA_ADAMW_MC_LAUNCH(G, M)                                                                                     \
+  adamw_kernel<G, M, true><<<(int)blocks, 256, 0, st>>>(master, m, v, grad, (bf16*)mc_param, n, lr, beta1, beta2, eps, \
+                                                        weight_decay, inv_bc1, inv_sqrt_bc2, grad_scale_dev, grad_prescale)
+  if (g32 && mom16) DLA_ADAMW_MC_LAUNCH(true, true);
+  else if (g32) DLA_ADAMW_MC_LAUNCH(true, false);
+  else if (mom16) DLA_ADAMW_MC_LAUNCH(false, true);
+  else DLA_ADAMW_MC_LAUNCH(false, false);
+#undef DLA_ADAMW_MC_LAUNCH
+  return check_launch("adamw_mc");
 }
 
 int dla_sumsq(const void* x, int64_t n, int is_fp32, float* scratch, float* out, int accumulate, void* stream) {

@@ -23,6 +23,7 @@ import os
 import random
 import shutil
 import threading
+import time
 from pathlib import Path
 from typing import Any, Dict, List, Optional
 
@@ -34,31 +35,47 @@ from dla_b200.parallel.engine import Engine
 from dla_b200.parallel.pg import DistContext
 
 
+def _snapshot_model(engine: Engine, ctx: DistContext, reward_bin: bool = False):
+    """Collective part of a model export: every rank takes part in the unit gathers, rank 0 ends up with the
+    HF-named tensors on the HOST (and the ``backbone.*`` / ``scorer.*`` state of the reward phase)."""
+    tensors: Dict[str, torch.Tensor] = {}
+    bin_state: Dict[str, torch.Tensor] = {}
+    for u in engine.units:
+        w = engine.gathered_unit(u.name)
+        if not ctx.is_main:
+            continue
+        for k, t in export_unit(engine.cfg, u.name, w).items():
+            t = t.detach().to("cpu").contiguous()
+            tensors[k] = t
+            if reward_bin:
+                if k.startswith("scorer."):
+                    bin_state[k] = t
+                else:
+                    kk = k.split(".", 1)[1] if k.split(".", 1)[0] in ("model", "transformer") else k
+                    bin_state["backbone." + kk] = t
+    return tensors, bin_state
+
+
+def _write_model(engine_cfg: Any, out_dir: Path, tensors: Dict[str, torch.Tensor], bin_state: Dict[str, torch.Tensor],
+                 tokenizer: Any, reward_bin: bool) -> None:
+    """File part (rank 0 only, no collectives): may run on the writer thread."""
+    writer = ShardedSafetensorsWriter(out_dir)
+    writer.add(tensors)
+    writer.close()
+    engine_cfg.save(out_dir)
+    if tokenizer is not None and hasattr(tokenizer, "save_pretrained"):
+        tokenizer.save_pretrained(str(out_dir))
+    if reward_bin:
+        torch.save(bin_state, out_dir / "pytorch_model.bin")
+
+
 def save_model_dir(engine: Engine, out_dir: Path, ctx: DistContext, tokenizer: Any = None,
                    reward_bin: bool = False) -> None:
     """Consolidated HF-style model directory.  Collective: every rank takes part in the unit gathers,
     rank 0 writes."""
-    writer = ShardedSafetensorsWriter(out_dir) if ctx.is_main else None
-    bin_state: Dict[str, torch.Tensor] = {}
-    for u in engine.units:
-        w = engine.gathered_unit(u.name)
-        if ctx.is_main:
-            tensors = export_unit(engine.cfg, u.name, w)
-            writer.add(tensors)
-            if reward_bin:
-                for k, t in tensors.items():
-                    if k.startswith("scorer."):
-                        bin_state[k] = t.cpu()
-                    else:
-                        kk = k.split(".", 1)[1] if k.split(".", 1)[0] in ("model", "transformer") else k
-                        bin_state["backbone." + kk] = t.cpu()
+    tensors, bin_state = _snapshot_model(engine, ctx, reward_bin)
     if ctx.is_main:
-        writer.close()
-        engine.cfg.save(out_dir)
-        if tokenizer is not None and hasattr(tokenizer, "save_pretrained"):
-            tokenizer.save_pretrained(str(out_dir))
-        if reward_bin:
-            torch.save(bin_state, out_dir / "pytorch_model.bin")
+        _write_model(engine.cfg, Path(out_dir), tensors, bin_state, tokenizer, reward_bin)
 
 
 def load_model_dir(engine: Engine, path: str | Path, strict: bool = False) -> int:
@@ -78,6 +95,7 @@ def load_model_dir(engine: Engine, path: str | Path, strict: bool = False) -> in
         if tensors:
             engine.load_unit(u.name, tensors)
             loaded += len(tensors)
+    engine.publish_shards()     # streamed fused engines: peers read these shards directly, make them visible first
     return loaded
 
 
@@ -97,11 +115,19 @@ def _set_rng_state(st: Dict[str, Any]) -> None:
 
 
 class CheckpointManager:
+    """``async_write=True`` splits a save into a snapshot (collective gathers + device -> host copies, done before
+    ``save`` returns, so training may overwrite the weights right away) and a write phase on a background thread
+    (serialisation, fsync-free file IO, the atomic rename, ``latest`` and pruning).  The thread uses no collective:
+    ranks signal completion with marker files and rank 0 finalises once every rank's marker exists.  ``wait()`` (also
+    called by the next ``save`` and by ``load``) joins it and re-raises its error."""
+
     def __init__(self, output_dir: str | Path, ctx: DistContext, keep_last_n: Optional[int] = None,
-                 async_write: bool = False) -> None:
+                 async_write: bool = False, finalize_timeout_s: float = 1800.0) -> None:
         self.root, self.ctx, self.keep = Path(output_dir), ctx, keep_last_n
         self.async_write = async_write
+        self.finalize_timeout_s = finalize_timeout_s
         self._thread: Optional[threading.Thread] = None
+        self._error: Optional[BaseException] = None
         if ctx.is_main:
             self.root.mkdir(parents=True, exist_ok=True)
 
@@ -117,32 +143,66 @@ class CheckpointManager:
                 shutil.rmtree(tmp)
             (tmp / "shards").mkdir(parents=True, exist_ok=True)
         self.ctx.barrier()
+        # ---- snapshot: everything that needs the device or a collective ---------------------------
         primary = primary or next((n for n, e in engines.items() if e.trainable), next(iter(engines)))
-        save_model_dir(engines[primary], tmp, self.ctx, tokenizer, reward_bin=reward_bin)
+        model_tensors, bin_state = _snapshot_model(engines[primary], self.ctx, reward_bin)
+        shard_states: Dict[str, Dict[str, torch.Tensor]] = {}
+        rng = None
         if save_optimizer:
+            for name, eng in engines.items():
+                if eng.trainable:
+                    shard_states[name] = {k: v.detach().cpu().contiguous().clone() if v.device.type == "cpu"
+                                          else v.detach().cpu().contiguous() for k, v in eng.shard_state().items()}
+            rng = _rng_state()
+        meta = {"world_size": self.ctx.world_size,
+                "engines": {n: {"sharding": e.sharding, "step_count": e.step_count, "trainable": e.trainable,
+                                "shard_group": e.W} for n, e in engines.items()}}
+        trainer_state = json.loads(json.dumps(trainer_state, default=str))      # frozen copy for the writer
+        cfg = engines[primary].cfg
+        rank, world, is_main = self.ctx.rank, self.ctx.world_size, self.ctx.is_main
+
+        # ---- write: files only, no collectives ------------------------------------------------------
+        def write() -> None:
             from safetensors.torch import save_file
 
-            for name, eng in engines.items():
-                if not eng.trainable:
-                    continue
-                state = {k: v.detach().cpu().contiguous() for k, v in eng.shard_state().items()}
-                save_file(state, str(tmp / "shards" / f"rank_{self.ctx.rank}.{name}.safetensors"))
-            torch.save(_rng_state(), tmp / "shards" / f"rng_{self.ctx.rank}.pt")
-        self.ctx.barrier()
-        if self.ctx.is_main:
-            meta = {"world_size": self.ctx.world_size,
-                    "engines": {n: {"sharding": e.sharding, "step_count": e.step_count, "trainable": e.trainable,
-                                    "shard_group": e.W} for n, e in engines.items()}}
+            for name, state in shard_states.items():
+                save_file(state, str(tmp / "shards" / f"rank_{rank}.{name}.safetensors"))
+            if rng is not None:
+                torch.save(rng, tmp / "shards" / f"rng_{rank}.pt")
+            if is_main:
+                _write_model(cfg, tmp, model_tensors, bin_state, tokenizer, reward_bin)
+            (tmp / "shards" / f".done_{rank}").touch()
+            if not is_main:
+                return
+            deadline = time.monotonic() + self.finalize_timeout_s
+            while not all((tmp / "shards" / f".done_{r}").exists() for r in range(world)):
+                if time.monotonic() > deadline:
+                    raise TimeoutError(f"checkpoint {tag}: not every rank finished writing within {self.finalize_timeout_s}s")
+                time.sleep(0.02)
+            for r in range(world):
+                (tmp / "shards" / f".done_{r}").unlink()
             with (tmp / "shards" / "meta.json").open("w") as fh:
                 json.dump(meta, fh, indent=2)
             with (tmp / "trainer_state.json").open("w") as fh:
-                json.dump(trainer_state, fh, indent=2, default=str)
+                json.dump(trainer_state, fh, indent=2)
             if out.exists():
                 shutil.rmtree(out)
             os.replace(tmp, out)
             self._point_latest(tag)
             self._prune()
-        self.ctx.barrier()
+
+        if self.async_write:
+            def guarded() -> None:
+                try:
+                    write()
+                except BaseException as e:  # surfaced by wait()
+                    self._error = e
+
+            self._thread = threading.Thread(target=guarded, name=f"ckpt-writer-{tag}", daemon=False)
+            self._thread.start()
+        else:
+            write()
+            self.ctx.barrier()
         return out
 
     def _point_latest(self, tag: str) -> None:
@@ -160,9 +220,13 @@ class CheckpointManager:
             shutil.rmtree(p, ignore_errors=True)
 
     def wait(self) -> None:
+        """Block until a background write (if any) has finished; raises what it raised."""
         if self._thread is not None:
             self._thread.join()
             self._thread = None
+        if self._error is not None:
+            e, self._error = self._error, None
+            raise RuntimeError(f"background checkpoint write failed: {e!r}") from e
 
     # ---------------------------------------------------------------- resume
     def resolve(self, resume: Optional[str]) -> Optional[Path]:
@@ -179,6 +243,7 @@ class CheckpointManager:
         """Exact resume when the shard files match this world size; otherwise weights only."""
         from safetensors.torch import load_file
 
+        self.wait()
         meta_p = path / "shards" / "meta.json"
         meta = json.load(meta_p.open()) if meta_p.exists() else None
         for name, eng in engines.items():

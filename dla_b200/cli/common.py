@@ -60,9 +60,11 @@ class TrainLoop:
             prepare_output_dirs(self.output_dir, self.log_dir)
         self.logger = MetricsLogger(self.log_dir, ctx.is_main, bool(log_cfg.get("use_wandb")), run_name=cfg.get("experiment_name"),
                                     config=cfg)
-        self.ckpt = CheckpointManager(self.output_dir, ctx, keep_last_n=log_cfg.get("keep_last_n"))
+        self.ckpt = CheckpointManager(self.output_dir, ctx, keep_last_n=log_cfg.get("keep_last_n"),
+                                      async_write=bool(log_cfg.get("async_checkpoint", False)))
         self.accum = plan.gradient_accumulation_steps
         self.global_step = 0          # micro-batches consumed (the reference's "step", defect D2)
+        self.micro_steps = 0          # micro_step() calls; accumulation boundaries count these (PPO runs several per step)
         self.optimizer_steps = 0
         self.epoch = 0
         self.running = RunningLoss()
@@ -81,6 +83,7 @@ class TrainLoop:
             if path is not None:
                 st = self.ckpt.load(path, {k: e for k, e in engines.items() if e.trainable})
                 self.global_step = int(st.get("global_step", 0))
+                self.micro_steps = int(st.get("micro_steps", self.global_step))
                 self.optimizer_steps = int(st.get("optimizer_steps", 0))
                 self.epoch = int(st.get("epoch", 0))
                 self.sampler_state = st.get("sampler", {}) or {}
@@ -92,7 +95,7 @@ class TrainLoop:
 
     def micro_step(self, loss_fn: Callable[[], torch.Tensor], batch: Any = None) -> torch.Tensor:
         """forward + backward of one micro-batch; optimizer update on accumulation boundaries."""
-        boundary = (self.global_step + 1) % self.accum == 0
+        boundary = (self.micro_steps + 1) % self.accum == 0
         self.engine.sync_grads = boundary
         with self.timer("fwd"):
             loss = loss_fn()
@@ -106,6 +109,7 @@ class TrainLoop:
                                            if self.engine.sharding != "none" else 1.0)
             self.optimizer_steps += 1
         self.global_step += 1
+        self.micro_steps += 1
         if self.tokens_fn is not None and batch is not None:
             self._tok_since += int(self.tokens_fn(batch))
         return loss.detach()
@@ -147,7 +151,8 @@ class TrainLoop:
             self.save(f"step_{self.global_step}", sampler)
 
     def trainer_state(self, sampler: Any = None) -> Dict[str, Any]:
-        st = {"phase": self.phase, "global_step": self.global_step, "optimizer_steps": self.optimizer_steps,
+        st = {"phase": self.phase, "global_step": self.global_step, "micro_steps": self.micro_steps,
+              "optimizer_steps": self.optimizer_steps,
               "epoch": self.epoch, "lr": self.current_lr(), "world_size": self.ctx.world_size}
         if sampler is not None and hasattr(sampler, "state_dict"):
             st["sampler"] = sampler.state_dict()
@@ -162,5 +167,6 @@ class TrainLoop:
 
     def finish(self, message: str, sampler: Any = None) -> None:
         self.save("final", sampler)
+        self.ckpt.wait()            # a background writer (logging.async_checkpoint) must finish before the process exits
         self.logger.close()
         self.ctx.print0(message)

@@ -32,7 +32,7 @@ from dla_b200.models.config import resolve_model_config
 from dla_b200.ops import functional as F
 from dla_b200.ops import reference as R
 from dla_b200.optim import AdamWConfig
-from dla_b200.rollout import Generator, decode_responses
+from dla_b200.rollout import Generator, decode_responses, splice_separator
 
 
 def load_prompts(cfg: Dict[str, Any]) -> List[str]:
@@ -44,7 +44,8 @@ def load_prompts(cfg: Dict[str, Any]) -> List[str]:
 
             ds = load_dataset(cfg["hf_path"], cfg.get("hf_name"), split=cfg.get("split", "train"), streaming=False)
             key = cfg.get("prompt_key", "prompt")
-            return [row[key] for row in ds if row.get(key)]
+            rows = [row[key] for row in ds if row.get(key)]
+            return rows[: int(cfg["limit"])] if cfg.get("limit") else rows      # ``limit`` is inert in the reference preset
         except Exception as e:
             fallback = cfg.get("prompt_path") or cfg.get("path")
             if not fallback:
@@ -93,6 +94,9 @@ def main() -> None:
     vhead = ValueHead(policy.engine) if algo == "ppo" else None
     tok = policy.tokenizer
     pad_id = getattr(tok, "pad_token_id", 0) or 0
+    sep_ids = tok("\n\n", add_special_tokens=False)["input_ids"] if same_tok else []
+    sep_ids = list(sep_ids[0]) if sep_ids and isinstance(sep_ids[0], (list, tuple)) else list(sep_ids)
+    fc = getattr(policy.engine, "fc", None) if (getattr(policy.engine, "fused", False) or getattr(policy.engine, "fused_ddp", False)) else None
     rng = random.Random(seed)
 
     while not loop.done():
@@ -108,7 +112,9 @@ def main() -> None:
         # ---- reward ---------------------------------------------------------------------------
         with torch.no_grad():
             if same_tok:
-                scores = reward_model(seqs, amask).float()
+                # the reward model scores "prompt\n\nresponse": splice the separator's ids in on the device
+                r_ids, r_mask = splice_separator(out, sep_ids, pad_id)
+                scores = reward_model(r_ids, r_mask).float()
             else:                                          # heterogeneous tokenizers: text round trip like the reference
                 texts = [f"{p}\n\n{r}" for p, r in zip(local_prompts, decode_responses(tok, out))]
                 renc = reward_tok(texts, return_tensors="pt", padding=True, truncation=True, max_length=max_len).to(ctx.device)
@@ -120,14 +126,24 @@ def main() -> None:
                 pol = sequence_logprobs(policy.model, seqs, amask)
                 with torch.no_grad():
                     refl = F.sequence_logprob(ref_tok_logp, amask[:, 1:])
+                if fc is not None and pol.is_cuda:
+                    # fused path (c): ONE kernel gathers (pol, ref, score) of every rank over peer memory and produces
+                    # the global baseline, the global kl / reward / score means and the local gradients
+                    from dla_b200.parallel.fused import fused_reinforce_loss
+
+                    loss, st = fused_reinforce_loss(fc, pol, refl, scores, kl_coef)
+                    info.update(kl=st[0], reward=st[1], score=st[2])
+                    return loss
+                with torch.no_grad():
                     rewards_local = scores - kl_coef * (pol.detach() - refl)
                     baseline = ctx.gather(rewards_local).mean()                      # global baseline
                 loss, kl, rewards = reinforce_step(pol, refl, scores, kl_coef, baseline)
-                info.update(kl=kl.detach().mean(), reward=rewards.detach().mean(), score=scores.mean())
+                glob = ctx.all_reduce(torch.stack([kl.detach().mean(), rewards.detach().mean(), scores.mean()]).float(), "mean")
+                info.update(kl=glob[0], reward=glob[1], score=glob[2])
                 return loss
             loss = loop.micro_step(loss_fn)
         else:
-            loss = _ppo_update(loop, policy, vhead, seqs, amask, out.response_mask, ref_tok_logp, scores, pc, kl_coef, info)
+            loss = _ppo_update(loop, policy, vhead, seqs, amask, out.response_mask, ref_tok_logp, scores, pc, kl_coef, info, ctx, fc)
         extra_log = {"train/kl": float(info["kl"].item()), "train/reward_mean": float(info["reward"].item()),
                      "train/score_mean": float(info["score"].item())} if loop.global_step % loop.log_every == 0 else None
         loop.after_step(loss, extra_log)
@@ -135,14 +151,24 @@ def main() -> None:
     loop.finish("RLHF PPO loop complete")
 
 
-def _ppo_update(loop, policy, vhead, seqs, amask, rmask, ref_tok_logp, scores, pc, kl_coef, info):
+def _ppo_update(loop, policy, vhead, seqs, amask, rmask, ref_tok_logp, scores, pc, kl_coef, info, ctx, fc=None):
     """Clipped PPO on the rollout batch: token rewards = -kl_coef * (logp - ref) with the sequence score on
-    the last response token, GAE, ``ppo.epochs`` x mini-batches, stop when approx-KL exceeds ``target_kl``."""
+    the last response token, GAE, ``ppo.epochs`` x mini-batches, stop when approx-KL exceeds ``target_kl``.
+
+    Everything that decides control flow is GLOBAL: the advantages are whitened with the mean / variance over all
+    ranks' tokens, kl / reward / score are logged as global means, every rank runs the same number of mini-batches
+    (rows beyond the smallest local batch are dropped) and the ``target_kl`` stop uses the maximum approx-KL over ranks —
+    each ``micro_step`` issues collectives, so a rank-local decision would desynchronise the job."""
     gamma, lam = float(pc.get("gamma", 1.0)), float(pc.get("lam", 0.95))
     clip, vclip, vf = float(pc.get("cliprange", 0.2)), float(pc.get("cliprange_value", 0.2)), float(pc.get("vf_coef", 0.5))
-    epochs, mbs = int(pc.get("epochs", 1)), int(pc.get("mini_batch_size", seqs.shape[0]))
+    epochs = int(pc.get("epochs", 1))
     target_kl = pc.get("target_kl")
-    m = rmask[:, 1:].float()
+    B = seqs.shape[0]
+    if ctx.distributed:
+        B = int(ctx.all_reduce(torch.tensor([B], device=seqs.device), "min").item())
+        seqs, amask, rmask, ref_tok_logp, scores = seqs[:B], amask[:B], rmask[:B], ref_tok_logp[:B], scores[:B]
+    mbs = max(1, min(int(pc.get("mini_batch_size", B)), B))
+    m = rmask[:, 1:].float().contiguous()
     with torch.no_grad():
         h = policy.model.hidden(seqs, amask)
         old_values = vhead(h)[:, :-1]
@@ -150,10 +176,26 @@ def _ppo_update(loop, policy, vhead, seqs, amask, rmask, ref_tok_logp, scores, p
         kl_tok = (old_logp - ref_tok_logp) * m
         rewards = -kl_coef * kl_tok
         last = (rmask.cumsum(1) * rmask).argmax(1).clamp(min=1) - 1
-        rewards[torch.arange(seqs.shape[0], device=seqs.device), last] += scores
-        adv, ret = F.gae(rewards, old_values * m, m, gamma, lam, whiten=True)      # one launch: scan + whitening
-    info.update(kl=(kl_tok.sum(1) / m.sum(1).clamp(min=1)).mean(), reward=rewards.sum(1).mean(), score=scores.mean())
-    B = seqs.shape[0]
+        rewards[torch.arange(B, device=seqs.device), last] += scores
+        local = torch.stack([(kl_tok.sum(1) / m.sum(1).clamp(min=1)).sum(), rewards.sum(1).sum(), scores.sum(),
+                             torch.tensor(float(B), device=seqs.device)]).float()
+        if fc is not None and seqs.is_cuda:
+            # fused path (c): GAE locally, then ONE kernel exchanges the whitening sums and the logged sums over peer
+            # memory and normalises the local advantages with the global statistics
+            adv, ret = F.gae(rewards, old_values * m, m, gamma, lam, whiten=False)
+            adv = adv.contiguous()
+            tot = fc.whiten_(adv, m, local)
+        elif ctx.distributed:
+            adv, ret = F.gae(rewards, old_values * m, m, gamma, lam, whiten=False)
+            sums = ctx.all_reduce(torch.cat([torch.stack([(adv * m).sum(), (adv * adv * m).sum(), m.sum()]).float(), local]), "sum")
+            mean = sums[0] / sums[2].clamp(min=1)
+            var = (sums[1] / sums[2].clamp(min=1) - mean * mean).clamp(min=0)
+            adv = (adv - mean) / var.sqrt().clamp(min=1e-6) * m
+            tot = sums[3:]
+        else:
+            adv, ret = F.gae(rewards, old_values * m, m, gamma, lam, whiten=True)      # one launch: scan + whitening
+            tot = local
+    info.update(kl=tot[0] / tot[3], reward=tot[1] / tot[3], score=tot[2] / tot[3])
     loss = torch.zeros((), device=seqs.device)
     stop = False
     step0 = loop.global_step                     # one reference "step" per rollout batch
@@ -174,12 +216,14 @@ def _ppo_update(loop, policy, vhead, seqs, amask, rmask, ref_tok_logp, scores, p
                 stats.update(st)
                 return l
             loss = loop.micro_step(loss_fn)
-            if target_kl is not None and float(stats["approx_kl"].item()) > float(target_kl):
-                stop = True
-                break
+            if target_kl is not None:
+                akl = ctx.all_reduce(stats["approx_kl"].detach().float().reshape(1).clone(), "max")
+                if float(akl.item()) > float(target_kl):
+                    stop = True
+                    break
         if stop:
             break
-    loop.global_step = step0 + 1
+    loop.global_step = step0 + 1       # the reference counts rollout batches; accumulation boundaries use loop.micro_steps
     return loss
 
 

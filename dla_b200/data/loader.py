@@ -39,7 +39,9 @@ def batch_nbytes(batch: Any) -> int:
 def build_loader(dataset: Dataset, micro_batch_size: int, world_size: int, rank: int,
                  shuffle: bool = True, num_workers: int = 0, seed: int = 0,
                  collate_fn: Optional[Callable] = None, drop_last: bool = False):
-    sampler = get_distributed_sampler(dataset, world_size, rank, shuffle=shuffle, seed=seed)  # type: ignore[arg-type]
+    # a single process gets a one-replica sampler too (the reference passes ``shuffle=True`` there): same seeded
+    # permutation every run, and the position inside the epoch becomes part of the checkpoint
+    sampler = get_distributed_sampler(dataset, world_size, rank, shuffle=shuffle, seed=seed, always=shuffle)  # type: ignore[arg-type]
     loader = DataLoader(
         dataset,
         batch_size=micro_batch_size,
@@ -100,15 +102,19 @@ def infinite_batches(loader: DataLoader, sampler: Optional[RankSampler]) -> Iter
     """Epoch loop of the reference (``for epoch in range(10_000): sampler.set_epoch(epoch)``,
     ``R/src/training/train_dpo.py:105-109``) as a generator of (epoch, batch)."""
     epoch = sampler.epoch if sampler is not None else 0
+    per_batch = int(getattr(getattr(loader, "loader", loader), "batch_size", None) or 1)
     while True:
         if sampler is not None:
             sampler.set_epoch(epoch)
         n = 0
+        base = sampler.start if sampler is not None else 0
         for batch in loader:
             n += 1
+            if sampler is not None:     # counted when handed out (a prefetcher may have staged one more batch already)
+                sampler.consumed = base + n * per_batch
             yield epoch, batch
         if n == 0:
             raise RuntimeError("dataset produced no batches")
         epoch += 1
         if sampler is not None:
-            sampler.start = 0
+            sampler.start = sampler.consumed = 0

@@ -30,7 +30,8 @@ class RankSampler(Sampler[int]):
         self.n = len(dataset)
         self.num_replicas, self.rank, self.shuffle, self.seed, self.drop_last = num_replicas, rank, shuffle, seed, drop_last
         self.epoch = 0
-        self.start = 0  # samples of this rank already consumed in the current epoch (resume)
+        self.start = 0  # samples of this rank skipped at the beginning of the current epoch (resume point)
+        self.consumed = 0  # samples of this rank handed to the training loop so far in the current epoch
         if drop_last and self.n % num_replicas:
             self.num_samples = self.n // num_replicas
         else:
@@ -39,7 +40,7 @@ class RankSampler(Sampler[int]):
 
     def set_epoch(self, epoch: int) -> None:
         if epoch != self.epoch:
-            self.start = 0
+            self.start = self.consumed = 0
         self.epoch = epoch
 
     def _order(self) -> list[int]:
@@ -64,17 +65,23 @@ class RankSampler(Sampler[int]):
         return self.num_samples - self.start
 
     def state_dict(self) -> Dict[str, Any]:
-        return {"epoch": self.epoch, "start": self.start, "seed": self.seed}
+        """``start`` is the number of this rank's samples the loop has already trained on in ``epoch``
+        (``infinite_batches`` advances ``consumed`` as it yields), so a resumed run skips exactly those."""
+        return {"epoch": self.epoch, "start": min(max(self.consumed, self.start), self.num_samples), "seed": self.seed}
 
     def load_state_dict(self, state: Dict[str, Any]) -> None:
         self.epoch, self.start = int(state.get("epoch", 0)), int(state.get("start", 0))
         self.seed = int(state.get("seed", self.seed))
+        if self.start >= self.num_samples:      # saved exactly at an epoch boundary
+            self.epoch, self.start = self.epoch + 1, 0
+        self.consumed = self.start
 
 
 def get_distributed_sampler(dataset: Sized, world_size: int, rank: int, shuffle: bool = True,
-                            seed: int = 0) -> Optional[RankSampler]:
-    """``None`` for a single process, else a rank partition (``R/src/training/utils.py:110-118``)."""
-    if world_size > 1:
+                            seed: int = 0, always: bool = False) -> Optional[RankSampler]:
+    """``None`` for a single process, else a rank partition (``R/src/training/utils.py:110-118``).  ``always=True``
+    also gives a single process a (one-replica) sampler so that its position in the epoch can be saved and resumed."""
+    if world_size > 1 or always:
         return RankSampler(dataset, world_size, rank, shuffle=shuffle, seed=seed)
     return None
 

@@ -80,15 +80,17 @@ def build_reward_model(base_model_name_or_path: str, ctx: DistContext, plan: Opt
     return model, tokenizer
 
 
-def freeze_except_lora(engine: Engine, lora_layers: Optional[str] = None) -> None:
-    """Substring-based freeze (``R/src/models/base_model.py:45-49``; dead code there).  Units with no
-    matching parameter stop producing gradients; matching is per parameter name."""
-    engine.frozen_filter = lora_layers  # consulted by optimizer_step via Engine.param_mask
+def freeze_except_lora(engine: Engine, lora_layers: Optional[str] = None) -> Dict[str, Any]:
+    """Substring-based freeze (``R/src/models/base_model.py:45-49``; dead code there): parameters whose qualified
+    name ``<unit>.<param>`` (e.g. ``layer.3.wqkv``) contains ``lora_layers`` stay trainable, all others are frozen —
+    ``None`` freezes everything, as in the reference.  Implemented by :meth:`Engine.freeze_except`: frozen gradients
+    are cleared before norm / reduction and AdamW (weight decay included) skips the frozen ranges of every shard."""
+    return engine.freeze_except(lora_layers)
 
 
 def count_trainable_params(engine: Engine) -> Dict[str, Any]:
     """total / trainable / ratio (``R/src/models/base_model.py:52-59``)."""
     total = engine.num_params()
-    trainable = total if engine.trainable else 0
+    trainable = engine.trainable_numel()
     return {"total_params": total, "trainable_params": trainable,
             "trainable_ratio": trainable / total if total else 0.0}

@@ -153,6 +153,10 @@ class ParamProvider:
     def grads_done(self, unit: str, weights: Weights) -> None:
         pass
 
+    def unit_backward_done(self, unit: str) -> None:
+        """A unit that kept its activations has finished its backward (see ``_UnitBoundary``)."""
+        pass
+
 
 class LocalParams(ParamProvider):
     """All parameters resident on one device, one flat buffer per unit (+ a flat grad buffer when
@@ -191,6 +195,9 @@ class LocalParams(ParamProvider):
 
     def grads_done(self, unit: str, weights: Weights) -> None:
         collect_autograd_grads(weights)
+
+    def unit_backward_done(self, unit: str) -> None:
+        collect_autograd_grads(self._views.get(unit, {}))
 
     # convenience -----------------------------------------------------------------------
     def zero_grad(self) -> None:
@@ -286,17 +293,44 @@ def _anchor(device: torch.device) -> torch.Tensor:
     return _ANCHORS[key]
 
 
+class _UnitBoundary(torch.autograd.Function):
+    """Identity on a unit's input whose backward tells the provider that the unit's weight gradients are final.
+
+    For units that keep their activations (plain autograd, no recompute) there is no per-unit backward call to hang
+    that signal on.  The node created here is older than every node of the unit, and every op of the unit sits on a
+    path from this input to the unit's outputs, so autograd runs it only after all of them — each of which wrote its
+    weight gradient inside its own backward — have run.  A sharded engine can then start that unit's reduce-scatter
+    while earlier layers are still in backward, exactly as for recomputed units."""
+
+    @staticmethod
+    def forward(ctx, x, provider, unit):
+        ctx.provider, ctx.unit = provider, unit
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.provider.unit_backward_done(ctx.unit)
+        return g, None, None
+
+
 def run_unit(provider: ParamProvider, unit: str, fn: Callable, *inputs):
     grad_mode = torch.is_grad_enabled() and provider.trainable
     if grad_mode and provider.checkpoint and unit not in provider.no_recompute:
         dev = next(t.device for t in inputs if isinstance(t, torch.Tensor))
         return _CheckpointedUnit.apply(provider, unit, fn, _anchor(dev), *inputs)
     w = provider.acquire(unit, backward=False)
+    hooked = False
+    if grad_mode:
+        for i, t in enumerate(inputs):
+            if isinstance(t, torch.Tensor) and t.is_floating_point() and t.requires_grad:
+                inputs = inputs[:i] + (_UnitBoundary.apply(t, provider, unit),) + inputs[i + 1:]
+                hooked = True
+                break
     out = fn(w, *inputs)
     if not grad_mode:
         provider.release(unit, backward=False)
-    else:
-        provider.note_plain(unit)       # activations stay alive for a plain autograd backward (no recompute)
+    elif not hooked:
+        provider.note_plain(unit)       # no differentiable input to hang the signal on: swept in finish_backward
     return out
 
 
@@ -415,25 +449,6 @@ class CausalLM:
         lp = self.token_logprobs(input_ids, attention_mask, labels=labels, **kw)
         valid = (labels[:, 1:] >= 0)
         return -(lp * valid).sum() / valid.sum().clamp(min=1)
-
-
-class _HeadDone(torch.autograd.Function):
-    """Identity whose backward fires ``provider.grads_done`` for units used outside ``run_unit``."""
-
-    @staticmethod
-    def forward(ctx, x, provider, unit):
-        ctx.provider, ctx.unit = provider, unit
-        return x.view_as(x)
-
-    @staticmethod
-    def backward(ctx, g):
-        return g, None, None
-
-
-def _register_head_done(t: torch.Tensor, provider: ParamProvider, unit: str) -> None:
-    # the lm_head weight-grad lands in its slot during linear_logprob's backward, which runs BEFORE the
-    # head unit's own backward; the head/embed unit's grads_done therefore covers it.
-    return None
 
 
 def build_causal_lm(name_or_cfg, device: torch.device | str = "cpu", dtype: Optional[torch.dtype] = None,

@@ -82,6 +82,10 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     return LIB
 
 
+def main() -> None:
+    """``python -m dla_b200.ops.build [--force] [-v]`` / the ``dla-build`` console script."""
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+
+
 if __name__ == "__main__":
-    path = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
-    print(path)
+    main()

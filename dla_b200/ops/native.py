@@ -67,6 +67,14 @@ _SIGNATURES = {
     "dla_peer_allreduce": [P, I, I, I64, I64, F, P],
     "dla_ag_gemm_bf16": [P, P, P, I64, I64, P, I, I, I, I64, I64, I, I, P, c_uint32, I, I, P],
     "dla_fused_gather_dpo": [P, P, I, I, P, P, P, P, I, F, F, c_uint32, P, P, P, P],
+    "dla_adamw_mc": [P, P, P, P, P, I64, F, F, F, F, F, F, F, P, F, I, P],
+    "dla_unit_reduce": [P, I, P, P, I, I, I64, I64, F, P, P, c_uint32, I, I, P],
+    "dla_peer_norm_clip": [P, P, I, I, P, F, F, c_uint32, I, P, P, P],
+    "dla_peer_push_mc": [P, P, I64, I64, P],
+    "dla_peer_allreduce_mc": [P, I, I, I64, I64, F, P],
+    "dla_peer_watch": [P],
+    "dla_fused_gather_reinforce": [P, P, I, I, P, P, P, I, F, c_uint32, P, P, P],
+    "dla_fused_gather_whiten": [P, P, I, I, P, P, I, P, I, c_uint32, P, P],
 }
 
 

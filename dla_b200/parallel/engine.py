@@ -127,6 +127,12 @@ class Engine(ParamProvider):
         self.lazy_zero = _os.environ.get("DLA_LAZY_ZERO", "1") != "0"
         self._all_ready: Optional["torch.cuda.Event"] = None
         self.sync_grads = True          # False on non-boundary accumulation micro-steps (``no_sync``)
+        # fused path (a) v2: each unit's reduce-scatter is launched on the side stream DURING backward, as soon as the
+        # unit's bucket is final, gated by per-unit flags instead of a global barrier (DLA_RS_IN_BACKWARD=0: legacy)
+        self.rs_in_backward = (self.fused and self.overlap_optimizer and _os.environ.get("DLA_RS_IN_BACKWARD", "1") != "0")
+        self._rs_epoch = 0
+        self._rs_launched: set = set()
+        self._train_ranges: Optional[Dict[str, List[tuple]]] = None     # set by freeze_except
         self.step_count = 0
         self._sumsq = None
         self._coef = None
@@ -147,6 +153,8 @@ class Engine(ParamProvider):
                 off += self.P[u.name]
             self.param_arena = SymmetricArena(self.ctx, off, self.dtype)
             self.grad_arena = SymmetricArena(self.ctx, off, self.grad_dtype)
+            self._flag_base = self.fc.claim_unit_rows(len(self.units))
+            self._unit_index = {u.name: i for i, u in enumerate(self.units)}
         if self.fused_ddp:
             from dla_b200.parallel.fused import SymmetricArena
 
@@ -184,6 +192,9 @@ class Engine(ParamProvider):
                     sb = self.sbase[u.name]
                     self.shard[u.name] = self.shard_arena.tensor[sb:sb + S]
                     self.shard[u.name].copy_(full[self.r * S:(self.r + 1) * S])
+                elif self.fused:
+                    # the rank's shard IS its slice of the resident copy: the multicast store of the update reaches it too
+                    self.shard[u.name] = full[self.r * S:(self.r + 1) * S]
                 else:
                     self.shard[u.name] = full[self.r * S:(self.r + 1) * S].clone()
                 self.full[u.name] = full if self.resident else None
@@ -387,7 +398,12 @@ class Engine(ParamProvider):
         else:
             self._launch_reduce(unit)               # streamed units reduce-scatter every micro-step
 
+    def unit_backward_done(self, unit: str) -> None:
+        self.grads_done(unit, self._views.get(unit, {}))
+
     def _launch_reduce(self, unit: str) -> None:
+        if self.fused and self.rs_in_backward:
+            return self._launch_unit_reduce(unit)
         if self.fused or self.fused_ddp:
             return          # peers pull this bucket themselves inside the fused kernels
         gb = self.gradbuf[unit]
@@ -402,6 +418,25 @@ class Engine(ParamProvider):
             self._reduce_work.append((work, unit, out))
             if not self.resident:
                 self._drain(keep=2)                 # bound live full-size grad buckets when streaming units
+
+    def _launch_unit_reduce(self, unit: str) -> None:
+        """Fused path (a) v2: this rank's bucket for ``unit`` is final (everything enqueued so far on the current
+        stream).  Queue the unit's reduce-scatter kernel on the side stream behind that point; the kernel itself
+        announces the bucket to the peers and waits for theirs, so earlier layers' backward keeps running meanwhile."""
+        if unit in self._rs_launched:
+            return
+        self._zero_frozen(unit)
+        if self._opt_stream is None:
+            self._opt_stream = torch.cuda.Stream(device=self.device)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._opt_stream.wait_event(ev)
+        S = self.S[unit]
+        with torch.cuda.stream(self._opt_stream):
+            self.fc.reduce_unit(self.grad_arena, self._flag_base + 16 * self._unit_index[unit], self._rs_epoch + 1,
+                                self.base[unit] + self.r * S, S, 1.0, self.gred[unit], self._sumsq)
+        self.stats["reduce_bytes"] += S * _bytes(self.grad_dtype) * (1 if self.grad_arena.mc_ptr else self.W - 1)
+        self._rs_launched.add(unit)
 
     def _drain(self, keep: int = 0) -> None:
         while len(self._reduce_work) > keep:
@@ -428,7 +463,7 @@ class Engine(ParamProvider):
         self._plain_used.clear()
         self._materialize_fresh()       # slices nobody wrote this step become real zeros before peers / reductions read them
         self._drain(0)
-        if self.fused and self.sync_grads:
+        if self.fused and self.sync_grads and not self.rs_in_backward:
             self.fc.barrier(0)      # every rank's gradient buckets are complete before anyone reads them
         if self.fused_ddp and self.sync_grads:
             self.fc.all_reduce_(self.grad_arena, 0, self._ddp_total)
@@ -450,6 +485,8 @@ class Engine(ParamProvider):
         Gradients in the buckets are SUMS over ranks and micro-steps; ``grad_divisor`` (world x
         accumulation steps) turns them into the mean the reference's DDP/accumulate produces."""
         assert self.trainable
+        if getattr(self, "fc", None) is not None:
+            self.fc.check()         # a flag wait timed out since the last step: stop before applying / saving anything
         lr = opt.lr if lr is None else lr
         self.step_count += 1
         t = self.step_count
@@ -476,6 +513,9 @@ class Engine(ParamProvider):
                 self._all_ready.record(self._opt_stream)
             return
         # ---- global grad norm -------------------------------------------------------
+        if self._train_ranges is not None:
+            for u in self.units:
+                self._zero_frozen(u.name, local=True)
         if cuda:
             s = N.stream_ptr(self.device)
             self._sumsq.zero_()
@@ -513,11 +553,7 @@ class Engine(ParamProvider):
             with torch.cuda.stream(self._opt_stream):
                 sp = N.stream_ptr(self.device)
                 for u in self.units:
-                    g = self._local_grad(u.name)
-                    sh = self.shard[u.name]
-                    N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]), N.ptr(g),
-                           N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef),
-                           prescale, int(g.dtype == torch.float32) | self._moment_flag, sp)
+                    self._adamw_cuda(u.name, self._local_grad(u.name), opt, lr, bc1, bc2, prescale, sp)
                     self._zero_unit(u.name)
                     e = torch.cuda.Event()
                     e.record(self._opt_stream)
@@ -527,13 +563,12 @@ class Engine(ParamProvider):
             g = self._local_grad(u.name)
             sh = self.shard[u.name]
             if cuda:
-                N.call("dla_adamw", N.ptr(self.master[u.name]), N.ptr(self.m[u.name]), N.ptr(self.v[u.name]), N.ptr(g),
-                       N.ptr(sh), sh.numel(), lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef),
-                       prescale, int(g.dtype == torch.float32) | self._moment_flag, N.stream_ptr(self.device))
-            else:
-                R.adamw_step(self.master[u.name], self.m[u.name], self.v[u.name], g, lr, b1, b2, opt.eps,
-                             opt.weight_decay, t, grad_scale=prescale * coef)
-                sh.copy_(self.master[u.name].to(sh.dtype))
+                self._adamw_cuda(u.name, g, opt, lr, bc1, bc2, prescale, N.stream_ptr(self.device))
+            elif coef != 0.0:       # coef 0 = non-finite gradient norm: skip the update, weight decay included
+                for lo, hi in self._ranges(u.name):
+                    R.adamw_step(self.master[u.name][lo:hi], self.m[u.name][lo:hi], self.v[u.name][lo:hi], g[lo:hi], lr, b1, b2,
+                                 opt.eps, opt.weight_decay, t, grad_scale=prescale * coef)
+                    sh[lo:hi].copy_(self.master[u.name][lo:hi].to(sh.dtype))
         # ---- refresh resident gathered params ----------------------------------------
         if self.W > 1 and self.resident:
             works = []
@@ -554,7 +589,31 @@ class Engine(ParamProvider):
         fc, s = self.fc, N.stream_ptr(self.device)
         b1, b2 = opt.betas
         clip_on = bool(opt.max_grad_norm and opt.max_grad_norm > 0)
-        if clip_on or self._moment_flag:        # the single-kernel reduce+AdamW keeps fp32 moments only
+        if self.rs_in_backward:
+            # v2: the per-unit reduce-scatters were queued on this stream during backward (units that never signalled
+            # are reduced now); what remains is the norm exchange, AdamW and the push of the updated shards
+            for u in self.units:
+                self._launch_unit_reduce(u.name)
+            self._rs_launched.clear()
+            self._rs_epoch += 1
+            fc.norm_clip(self._sumsq, prescale, float(opt.max_grad_norm or 0.0), self._coef, self._norm)
+            self._last_grad_norm = self._norm
+            mc = self.param_arena.mc_ptr
+            esz = _bytes(self.dtype)
+            for u in self.units:
+                sh, off = self.shard[u.name], self.base[u.name] + self.r * self.S[u.name]
+                for lo, hi in self._ranges(u.name):
+                    args = (N.ptr(self.master[u.name]) + 4 * lo, N.ptr(self.m[u.name]) + self.m[u.name].element_size() * lo,
+                            N.ptr(self.v[u.name]) + self.v[u.name].element_size() * lo, N.ptr(self.gred[u.name]) + 4 * lo)
+                    tail = (hi - lo, lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2, N.ptr(self._coef), prescale,
+                            1 | self._moment_flag, s)
+                    if mc:      # one multicast store per 16 bytes updates every rank's resident copy (mine included)
+                        N.call("dla_adamw_mc", *args, mc + (off + lo) * esz, *tail)
+                    else:
+                        N.call("dla_adamw", *args, N.ptr(sh) + esz * lo, *tail)
+                        fc.push_shard(sh[lo:hi], self.param_arena, off + lo)
+                    self.stats["allgather_bytes"] += (hi - lo) * esz * (1 if mc else self.W - 1)
+        elif clip_on or self._moment_flag:        # the single-kernel reduce+AdamW keeps fp32 moments only
             self._sumsq.zero_()
             for u in self.units:
                 off = self.base[u.name] + self.r * self.S[u.name]
@@ -578,6 +637,97 @@ class Engine(ParamProvider):
             self._last_grad_norm = None
         fc.barrier(0)               # all peers finished reading my gradients and writing my parameters
         self.zero_grad()
+
+    def _ranges(self, unit: str) -> List[tuple]:
+        """Shard-local element ranges the optimizer updates: everything, unless :meth:`freeze_except` narrowed it."""
+        if self._train_ranges is None:
+            return [(0, self.shard[unit].numel())]
+        return self._train_ranges[unit]
+
+    def _adamw_cuda(self, unit: str, g: torch.Tensor, opt: AdamWConfig, lr: float, bc1: float, bc2: float, prescale: float,
+                    stream: int) -> None:
+        sh, b1, b2 = self.shard[unit], opt.betas[0], opt.betas[1]
+        gsz, msz, esz = g.element_size(), self.m[unit].element_size(), sh.element_size()
+        for lo, hi in self._ranges(unit):
+            N.call("dla_adamw", N.ptr(self.master[unit]) + 4 * lo, N.ptr(self.m[unit]) + msz * lo, N.ptr(self.v[unit]) + msz * lo,
+                   N.ptr(g) + gsz * lo, N.ptr(sh) + esz * lo, hi - lo, lr, b1, b2, opt.eps, opt.weight_decay, bc1, bc2,
+                   N.ptr(self._coef), prescale, int(g.dtype == torch.float32) | self._moment_flag, stream)
+
+    def freeze_except(self, substring: Optional[str]) -> Dict[str, int]:
+        """Only parameters whose qualified name ``<unit>.<param>`` contains ``substring`` stay trainable; ``None`` or
+        no match freezes everything (``freeze_except_lora``, ``R/src/models/base_model.py:45-49``).  Frozen parameters
+        keep their values exactly: their gradients are cleared before the norm and the reduction, and AdamW (weight
+        decay included) runs only over the trainable ranges of each shard.  ``freeze_except("")`` undoes it."""
+        if substring == "":
+            self._train_ranges = None
+            return {"trainable_params": self.num_params(), "total_params": self.num_params()}
+        ranges: Dict[str, List[tuple]] = {}
+        frozen: Dict[str, List[tuple]] = {}
+        n_train = 0
+        for u in self.units:
+            S = self.shard[u.name].numel()
+            lo_s = self.r * S if self.W > 1 else 0
+            keep: List[tuple] = []
+            drop: List[tuple] = []
+            for prm in u.params:
+                o, n = u.offsets()[prm.name]
+                e = o + -(-n // 8) * 8
+                hit = bool(substring) and substring in f"{u.name}.{prm.name}"
+                n_train += n if hit else 0
+                (keep if hit else drop).append((o, e))
+            frozen[u.name] = drop
+            loc: List[tuple] = []
+            for o, e in keep:
+                a, b = max(o, lo_s) - lo_s, min(e, lo_s + S) - lo_s
+                if a < b:
+                    if loc and loc[-1][1] == a:
+                        loc[-1] = (loc[-1][0], b)
+                    else:
+                        loc.append((a, b))
+            ranges[u.name] = loc
+        self._train_ranges, self._frozen_full = ranges, frozen
+        return {"trainable_params": n_train, "total_params": self.num_params()}
+
+    def trainable_numel(self) -> int:
+        if not self.trainable:
+            return 0
+        if self._train_ranges is None:
+            return self.num_params()
+        tot = 0
+        for u in self.units:
+            offs = u.offsets()
+            fro = {o for o, _ in self._frozen_full[u.name]}
+            tot += sum(p.numel for p in u.params if offs[p.name][0] not in fro)
+        return tot
+
+    def _zero_frozen(self, unit: str, local: bool = False) -> None:
+        """Clear the gradients of frozen parameters: in the full-size bucket before it is reduced, or (``local``) in
+        whatever tensor this rank's optimizer shard reads."""
+        if self._train_ranges is None:
+            return
+        if local:
+            g = self._local_grad(unit)
+            if g is None:
+                return
+            prev = 0
+            for lo, hi in self._train_ranges[unit] + [(g.numel(), g.numel())]:
+                if prev < lo:
+                    g[prev:lo].zero_()
+                prev = hi
+            return
+        gb = self.gradbuf.get(unit)
+        if gb is None:
+            return
+        for o, e in self._frozen_full[unit]:
+            gb[o:min(e, gb.numel())].zero_()
+
+    def publish_shards(self) -> None:
+        """Streamed fused mode: peers pull this rank's parameter shards straight out of the symmetric arena inside their
+        GEMMs, so after ANY host-driven overwrite of the shards (pretrained load, resume) every rank's copies must
+        have landed before anyone's next forward.  No-op otherwise."""
+        if self.fused_stream:
+            torch.cuda.synchronize(self.device)
+            self.ctx.barrier()
 
     def zero_grad(self) -> None:
         if torch.cuda.is_available() and self.device.type == "cuda" and torch.cuda.current_stream(self.device) != self._opt_stream:
@@ -671,7 +821,9 @@ class Engine(ParamProvider):
         self.step_count = step_count
         if self.W > 1 and self.resident:
             for u in self.units:
-                dist.all_gather_into_tensor(self.full[u.name], self.shard[u.name], group=self.ctx.group)
+                src = self.shard[u.name].clone() if self.fused else self.shard[u.name]   # fused: the shard aliases ``full``
+                dist.all_gather_into_tensor(self.full[u.name], src, group=self.ctx.group)
+        self.publish_shards()
 
     def memory_report(self) -> Dict[str, float]:
         gb = 1 / (1 << 30)

@@ -11,7 +11,7 @@ directly by its continuation, right-padded with ``pad_token_id``.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import List, Optional
+from typing import Sequence, List, Optional
 
 import torch
 
@@ -437,6 +437,29 @@ def sample(logits: torch.Tensor, temperature: float, top_p: float, generator: Op
     if temperature <= 0:
         return logits.argmax(-1)
     return R.top_p_sample(logits, temperature, top_p, generator)
+
+
+def splice_separator(out: GenerationOutput, sep_ids: Sequence[int], pad_id: int = 0):
+    """``(ids, mask)`` of ``prompt + sep + response`` per row, built on the device from a rollout's right-padded
+    ``prompt + response`` rows.  The reward model is trained on ``f"{prompt}\n\n{completion}"`` and the reference
+    scores rollouts through that text form (``R/src/training/train_rlhf.py:139-147``); when policy and reward model
+    share a tokenizer the same token sequence is produced here without the decode / re-tokenise round trip."""
+    seqs, plen, lens = out.sequences, out.prompt_lens.long(), out.lengths.long()
+    k = len(sep_ids)
+    if k == 0:
+        return seqs, out.attention_mask
+    B, L = seqs.shape
+    dev = seqs.device
+    sep = torch.tensor(list(sep_ids), dtype=seqs.dtype, device=dev)
+    j = torch.arange(L + k, device=dev)[None, :]
+    p = plen[:, None]
+    src = torch.where(j < p, j, j - k).clamp_(0, L - 1)
+    ids = seqs.gather(1, src.expand(B, L + k))
+    in_sep = (j >= p) & (j < p + k)
+    ids = torch.where(in_sep, sep[(j - p).clamp(0, k - 1)], ids)
+    mask = (j < (lens[:, None] + k))
+    ids = torch.where(mask, ids, torch.full_like(ids, pad_id))
+    return ids, mask.to(out.attention_mask.dtype)
 
 
 def decode_responses(tokenizer, out: GenerationOutput) -> List[str]:

@@ -96,6 +96,13 @@ int dla_adamw(float* master, void* m, void* v, const void* grad, void* param, in
               float lr, float beta1, float beta2, float eps, float weight_decay,
               float bias_c1, float bias_c2, const float* grad_scale_dev, float grad_prescale,
               int flags, void* stream);
+/* As dla_adamw, but `mc_param` is the NVSwitch MULTICAST address of the rank's shard inside the symmetric parameter
+ * arena: each 16-byte result is written with one multimem.st and lands in every rank's resident copy, so no all-gather
+ * follows the step.  n % 8 == 0.  R: the post-step parameter all-gather of FSDP/ZeRO-3. */
+int dla_adamw_mc(float* master, void* m, void* v, const void* grad, void* mc_param, int64_t n,
+                 float lr, float beta1, float beta2, float eps, float weight_decay,
+                 float bias_c1, float bias_c2, const float* grad_scale_dev, float grad_prescale,
+                 int flags, void* stream);
 /* out[0] (+)= sum(x^2). scratch: fp32 [dla_sumsq_blocks()].  R: clip_grad_norm_ at
  * R/src/training/utils.py:121-123. */
 int dla_sumsq(const void* x, int64_t n, int is_fp32, float* scratch, float* out, int accumulate,
@@ -296,13 +303,55 @@ int dla_ag_gemm_bf16(const void* A, const void* const* peer_shards, void* unit_f
  * small non-GEMM parameters of a streamed unit. */
 int dla_peer_gather(const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t offset, int64_t n,
                     int world, void* stream);
+/* (a) v2 — one unit's gradient reduce-scatter, meant to be launched on a side stream DURING backward as soon as this
+ * rank's bucket for the unit is final.  The unit owns `world` flag words at pads[*] + flag_word: block 0 publishes
+ * `epoch` to every peer, all blocks wait for all ranks' flags (timeout_ms of wall time, 0 = forever), then the rank's
+ * shard [shard_offset, +shard_elems) is summed into grad_out_fp32 (x scale) and sum(out^2) is added to sumsq_out
+ * (nullable).  mc_grads != NULL: the sum is done inside NVSwitch by multimem.ld_reduce on the multicast address of
+ * the gradient arena (bf16 result, fp32 accumulation); else W peer loads from peer_grads.  max_blocks <= 0: 2 per SM.
+ * R: the bucketed reduce-scatter DeepSpeed/FSDP overlap with backward (R/config/deepspeed_zero3.json:13-14,
+ * R/src/training/train_dpo.py:118). */
+int dla_unit_reduce(uint32_t* const* pads, int flag_word, const void* mc_grads, const void* const* peer_grads,
+                    int world, int rank, int64_t shard_elems, int64_t shard_offset, float scale,
+                    float* grad_out_fp32, float* sumsq_out, uint32_t epoch, int timeout_ms, int max_blocks,
+                    void* stream);
+/* Global grad-norm + clip coefficient without an NCCL launch: exchanges every rank's partial sum(g^2) over peer memory
+ * (bufs: per-rank fp32 [2][world]), sums in rank order, writes norm = sqrt(total) * prescale and
+ * coef = min(1, max_norm / (norm + 1e-6)) (0 when non-finite), and resets *sumsq_local to 0.
+ * R: clip_grad_norm_'s all-reduce (R/src/training/utils.py:121-123). */
+int dla_peer_norm_clip(float* const* bufs, uint32_t* const* pads, int world, int rank, float* sumsq_local,
+                       float prescale, float max_norm, uint32_t epoch, int channel, float* coef, float* norm_out,
+                       void* stream);
+/* All-gather by multicast stores: src[0..n) (bf16) -> element offset dst_offset of EVERY rank's copy (mc_dst is the
+ * multicast base address of the symmetric buffer). */
+int dla_peer_push_mc(const void* src, void* mc_dst, int64_t dst_offset, int64_t n, void* stream);
+/* dla_peer_allreduce through the switch: multimem.ld_reduce of this rank's slice + multimem.st of the result. */
+int dla_peer_allreduce_mc(void* mc, int world, int rank, int64_t offset, int64_t n, float scale, void* stream);
+/* Mirror the "a peer-flag wait timed out" bit into a word of pinned (device-mapped) host memory so that the training
+ * loop can poll it every step without synchronising the device.  NULL switches the mirror off. */
+int dla_peer_watch(void* host_mapped_word);
 /* (c) cross-rank all-gather of per-sequence log-probs fused with the DPO loss: each rank writes its
- * [4, B] block into every peer's gather buffer, barriers, then reduces loss / preference rate /
- * margin over all W*B pairs and produces its local gradients. */
+ * [4, B] block into every peer's gather buffer (fp32 [2][world][4][1024], half = epoch parity), exchanges flags, then
+ * reduces loss / preference rate / margin over all W*B pairs and produces its local gradients. */
 int dla_fused_gather_dpo(float* const* peer_bufs, uint32_t* const* pads, int world, int rank,
                          const float* pol_pos, const float* pol_neg, const float* ref_pos,
                          const float* ref_neg, int B, float beta, float label_smoothing,
                          uint32_t epoch, float* out, float* dpol_pos, float* dpol_neg, void* stream);
+
+/* (c) for the RLHF phase, sequence-level REINFORCE over the GLOBAL rollout batch: gathers every rank's
+ * (policy log-prob, reference log-prob, score) [3, B] block over peer memory (peer_bufs: fp32 [2][world][3][1024]) and
+ * computes r = score - kl_coef * (pol - ref), the global baseline mean(r), out = {loss, mean kl, mean r, mean score,
+ * baseline} over all W*B sequences and dpol[B] = -(r - baseline) / B for the local ones.
+ * R: R/src/training/train_rlhf.py:149-153 (rank-local there). */
+int dla_fused_gather_reinforce(float* const* peer_bufs, uint32_t* const* pads, int world, int rank, const float* pol,
+                               const float* ref, const float* score, int B, float kl_coef, uint32_t epoch,
+                               float* out, float* dpol, void* stream);
+/* (c) for clipped PPO: advantage whitening with GLOBAL mean / variance.  Each rank contributes the masked sums of its
+ * adv[n] (and up to 13 extra per-rank sums in `stats`, returned summed over ranks in stats_out), then normalises adv
+ * in place.  bufs: fp32 [2][world][16].  R: the `ppo.*` keys of R/config/rlhf_config.yaml:12-22. */
+int dla_fused_gather_whiten(float* const* bufs, uint32_t* const* pads, int world, int rank, float* adv,
+                            const float* mask, int n, const float* stats, int nstats, uint32_t epoch,
+                            float* stats_out, void* stream);
 
 /* Tiny all-gather over peer memory (eval losses, per-rank statistics): out[r*n + i] = rank r's src[i].  bufs: device
  * array of per-rank fp32 buffers [2][world][nmax] (the half is picked by the epoch parity); pads/channel/epoch as

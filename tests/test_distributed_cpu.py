@@ -142,6 +142,98 @@ def _ckpt_worker(rank, world, port, root):
     shutdown()
 
 
+def _async_ckpt_worker(rank, world, port, root):
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    sys.path.insert(0, str(ROOT))
+    torch.set_num_threads(2)
+    from dla_b200.ckpt import CheckpointManager
+    from dla_b200.data import ByteTokenizer
+    from dla_b200.models import build_units, resolve_model_config
+    from dla_b200.optim import AdamWConfig
+    from dla_b200.parallel.engine import Engine
+    from dla_b200.parallel.pg import init_distributed, shutdown
+
+    ctx = init_distributed(device="cpu")
+    cfg = resolve_model_config("tiny-llama")
+    units = build_units(cfg)
+    eng = Engine(cfg, units, ctx, sharding="zero3", dtype=torch.float32, seed=3, resident=False, name="policy")
+    mgr = CheckpointManager(root, ctx, keep_last_n=2, async_write=True)
+    snaps = {}
+    for step in (1, 2, 3):
+        for u in units:
+            eng.gshard[u.name].normal_(generator=torch.Generator().manual_seed(100 * step + rank))
+        eng.optimizer_step(AdamWConfig(lr=1e-2), grad_divisor=1.0)
+        snaps[step] = {u.name: eng.master[u.name].clone() for u in units}
+        mgr.save(f"step_{step}", {"policy": eng}, {"global_step": step}, tokenizer=ByteTokenizer(512))
+        # training goes on while the writer thread works: the snapshot must not see these later updates
+    mgr.wait()
+    ctx.barrier()
+    eng2 = Engine(cfg, units, ctx, sharding="zero3", dtype=torch.float32, seed=99, resident=False, name="policy")
+    state = mgr.load(mgr.resolve("latest"), {"policy": eng2})
+    assert state["global_step"] == 3 and eng2.step_count == 3
+    for u in units:
+        assert torch.equal(eng2.master[u.name], snaps[3][u.name])
+    eng3 = Engine(cfg, units, ctx, sharding="zero3", dtype=torch.float32, seed=98, resident=False, name="policy")
+    mgr.load(Path(root) / "step_2", {"policy": eng3})
+    for u in units:
+        assert torch.equal(eng3.master[u.name], snaps[2][u.name])
+    shutdown()
+
+
+@pytest.mark.timeout(600)
+def test_async_checkpoint_snapshots_then_writes_in_the_background(tmp_path):
+    """``CheckpointManager(async_write=True)``: ``save`` returns after the snapshot, files appear from the writer thread,
+    each checkpoint holds the state of ITS step although training continued, and the directory is complete after wait()."""
+    root = tmp_path / "ckpt"
+    mp.spawn(_async_ckpt_worker, args=(2, _free_port(), str(root)), nprocs=2, join=True)
+    names = sorted(p.name for p in root.iterdir())
+    assert names == ["latest", "step_2", "step_3"], names
+    assert os.readlink(root / "latest") == "step_3"
+    assert not list((root / "step_3" / "shards").glob(".done_*"))
+
+
+def _resume_other_world_worker(rank, world, port, root):
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    sys.path.insert(0, str(ROOT))
+    torch.set_num_threads(2)
+    from dla_b200.ckpt import CheckpointManager
+    from dla_b200.models import build_units, resolve_model_config
+    from dla_b200.parallel.engine import Engine
+    from dla_b200.parallel.pg import init_distributed, shutdown
+
+    ctx = init_distributed(device="cpu")
+    cfg = resolve_model_config("tiny-llama")
+    units = build_units(cfg)
+    eng = Engine(cfg, units, ctx, sharding="zero3", dtype=torch.float32, seed=1234, resident=False, name="policy")
+    mgr = CheckpointManager(root, ctx)
+    state = mgr.load(mgr.resolve("latest"), {"policy": eng})
+    assert state["global_step"] == 3
+    full = {u.name: {k: v.clone() for k, v in eng.gathered_unit(u.name).items()} for u in units}
+    if rank == 0:
+        torch.save(full, Path(root) / f"loaded_world{world}.pt")
+    shutdown()
+
+
+@pytest.mark.timeout(900)
+def test_checkpoint_written_at_world_2_loads_at_world_1_and_3(tmp_path):
+    """A step-N checkpoint is loadable at a DIFFERENT world size: the shard files no longer match, so the weights come
+    from the consolidated HF-named safetensors (optimizer state restarts)."""
+    root = tmp_path / "ckpt"
+    mp.spawn(_ckpt_worker, args=(2, _free_port(), str(root)), nprocs=2, join=True)
+    for world in (1, 3):
+        mp.spawn(_resume_other_world_worker, args=(world, _free_port(), str(root)), nprocs=world, join=True)
+    a, b = torch.load(root / "loaded_world1.pt"), torch.load(root / "loaded_world3.pt")
+    from safetensors.torch import load_file
+
+    ref = load_file(str(root / "final" / "model.safetensors"))
+    n = 0
+    for unit in a:
+        for k in a[unit]:
+            assert torch.equal(a[unit][k], b[unit][k]), (unit, k)
+            n += a[unit][k].numel()
+    assert n == sum(t.numel() for t in ref.values())
+
+
 @pytest.mark.timeout(600)
 def test_checkpoint_layout_roundtrip_and_keep_last_n(tmp_path):
     root = tmp_path / "ckpt"
