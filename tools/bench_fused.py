@@ -98,6 +98,54 @@ out["a_reduce_scatter_norm"] = {"unit_elems": P, "fused_ms": t_fa, "nccl_ms": t_
 out["a_reduce_adamw_allgather"] = {"fused_ms": t_faf, "nccl_ms": t_naf, "roofline_ms": roof_af,
                                    "fused_frac_of_roofline": roof_af / t_faf, "nccl_frac_of_roofline": roof_af / t_naf}
 
+# ---- (a) v2: flag-gated per-unit reduce-scatter (no barrier), in-switch sum vs P2P pull; AdamW with multicast store
+row0 = fc.claim_unit_rows(2)
+ep_v2 = [0, 0]
+os.environ["DLA_NO_MULTICAST"] = "1"
+grads_p2p = SymmetricArena(ctx, P, torch.bfloat16)
+os.environ.pop("DLA_NO_MULTICAST")
+grads_p2p.tensor.copy_(grads.tensor)
+coef, norm = torch.ones(1, device=dev), torch.zeros(1, device=dev)
+
+
+def v2_rs_switch():
+    ep_v2[0] += 1
+    fc.reduce_unit(grads, row0, ep_v2[0], r * S, S, 1.0, gred, sumsq)
+
+
+def v2_rs_p2p():
+    ep_v2[1] += 1
+    fc.reduce_unit(grads_p2p, row0 + 16, ep_v2[1], r * S, S, 1.0, gred, sumsq)
+
+
+def v2_full():
+    ep_v2[0] += 1
+    fc.reduce_unit(grads, row0, ep_v2[0], r * S, S, 1.0, gred, sumsq)
+    fc.norm_clip(sumsq, 1.0 / W, 1.0, coef, norm)
+    if params.mc_ptr:
+        N.call("dla_adamw_mc", N.ptr(master), N.ptr(m_), N.ptr(v_), N.ptr(gred), params.mc_ptr + r * S * 2, S, 1e-6, 0.9, 0.999, 1e-8,
+               0.01, 0.1, 0.001, N.ptr(coef), 1.0 / W, 1, N.stream_ptr())
+    else:
+        N.call("dla_adamw", N.ptr(master), N.ptr(m_), N.ptr(v_), N.ptr(gred), N.ptr(shard_bf16), S, 1e-6, 0.9, 0.999, 1e-8, 0.01,
+               0.1, 0.001, N.ptr(coef), 1.0 / W, 1, N.stream_ptr())
+        fc.push_shard(shard_bf16, params, r * S)
+    fc.barrier(0)
+
+
+t_v2s = timed(v2_rs_switch) if grads.mc_ptr else None
+t_v2p = timed(v2_rs_p2p)
+t_v2f = timed(v2_full)
+# with the sum done in the switch each rank still SENDS its (W-1) foreign shards (same egress bytes as the pull model) but
+# receives one reduced shard instead of W-1; the all-gather by multicast store is the mirror image (sends S, receives
+# (W-1) S).  A reduce-scatter and an all-gather in flight together therefore load each direction with W*S elements.
+out["a_v2_unit_reduce"] = {"multicast": bool(grads.mc_ptr), "switch_ms": t_v2s, "p2p_ms": t_v2p, "nccl_ms": t_na,
+                           "egress_bytes": link_bytes, "ingress_bytes_switch": S * 2, "ingress_bytes_p2p": link_bytes,
+                           "roofline_ms": roof_a, "switch_frac_of_roofline": (roof_a / t_v2s) if t_v2s else None,
+                           "p2p_frac_of_roofline": roof_a / t_v2p}
+out["a_v2_reduce_norm_adamw_push"] = {"ms": t_v2f, "legacy_fused_ms": t_faf, "nccl_ms": t_naf, "roofline_ms": roof_af,
+                                      "frac_of_roofline": roof_af / t_v2f,
+                                      "bytes_per_direction": {"out": link_bytes + S * 2, "in": S * 2 + link_bytes}}
+
 # ---------------------------------------------------------------- (b)
 bf16_tflops = 1632.6
 try:
