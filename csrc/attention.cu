@@ -351,8 +351,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   const int kv0 = j * BKV;
   int len = p.T;
   if (p.seqlens != nullptr) len = min(len, p.seqlens[b]);
-  const int nq = (len + BQ - 1) / BQ;
+  int nq = (len + BQ - 1) / BQ;
   const int i_begin = p.causal ? j : 0;
+  if (p.seg_start != nullptr) {
+    // packed rows: query tiles whose FIRST row's document starts after this kv tile see none of its keys, and
+    // neither does any later tile (seg_start is non-decreasing)
+    int i_end = i_begin;
+    while (i_end < nq && p.seg_start[(int64_t)b * p.T + i_end * BQ] <= kv0 + BKV - 1) ++i_end;
+    nq = i_end;
+  }
   const int iters_per_head = (kv0 < len && nq > i_begin) ? (nq - i_begin) : 0;
   const int n_iters = iters_per_head * G;
 
@@ -468,12 +475,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         neg_lse2 = -p.lse[o] * kLog2e;
         dlt = p.delta[o];
       }
-      const bool need_mask = (p.causal && (kv0 + BKV - 1 > q0)) || (kv0 + BKV > len) || (q0 + BQ > len);
-      int limit = 64;
+      int tile_lo = 0, row_lo = 0;
+      if (p.seg_start != nullptr) {
+        tile_lo = p.seg_start[(int64_t)b * p.T + min(q0 + BQ - 1, max(len - 1, 0))];     // largest start in this query tile
+        if (row_valid) row_lo = p.seg_start[(int64_t)b * p.T + q_idx];
+      }
+      const bool need_mask = (p.causal && (kv0 + BKV - 1 > q0)) || (kv0 + BKV > len) || (q0 + BQ > len) || (kv0 < tile_lo);
+      int limit = 64, lo = 0;                      // valid columns of this thread's 64: [lo, limit)
       if (need_mask) {
         int lim = len;
         if (p.causal) lim = min(lim, q_idx + 1);
         limit = row_valid ? lim - (kv0 + wg * 64) : 0;
+        lo = row_lo - (kv0 + wg * 64);
       }
       tc::mbar_wait(sdp_full, it & 1);
       tc::tc_fence_after();
@@ -504,8 +517,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (int jj = 0; jj < 32; jj += 2) {
             const int e = ch * 32 + jj;
-            const float p0 = e < limit ? ex2_approx(fmaf(__uint_as_float(s[jj]), scale2, neg_lse2)) : 0.f;
-            const float p1 = e + 1 < limit ? ex2_approx(fmaf(__uint_as_float(s[jj + 1]), scale2, neg_lse2)) : 0.f;
+            const float p0 = (e < limit && e >= lo) ? ex2_approx(fmaf(__uint_as_float(s[jj]), scale2, neg_lse2)) : 0.f;
+            const float p1 = (e + 1 < limit && e + 1 >= lo) ? ex2_approx(fmaf(__uint_as_float(s[jj + 1]), scale2, neg_lse2)) : 0.f;
             const float d0 = p0 * (__uint_as_float(dp[jj]) - dlt) * p.scale;
             const float d1 = p1 * (__uint_as_float(dp[jj + 1]) - dlt) * p.scale;
             pk[jj >> 1] = pack_bf16x2(p0, p1);
@@ -670,7 +683,17 @@ int dla_attn_set_fwd_variant(int v) {
 int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int B, int T, int Hq, int Hk, int D,
                  int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh, int64_t o_sb,
                  int64_t o_st, int64_t o_sh, const int32_t* seqlens, float scale, int causal, void* stream) {
+  return dla_attn_fwd_seg(q, k, v, o, lse, B, T, Hq, Hk, D, q_sb, q_st, q_sh, kv_sb, kv_st, kv_sh, o_sb, o_st, o_sh, seqlens,
+                          nullptr, scale, causal, stream);
+}
+
+int dla_attn_fwd_seg(const void* q, const void* k, const void* v, void* o, float* lse, int B, int T, int Hq, int Hk, int D,
+                     int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh, int64_t o_sb,
+                     int64_t o_st, int64_t o_sh, const int32_t* seqlens, const int32_t* seg_start, float scale, int causal,
+                     void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(seg_start == nullptr || (causal && g_fwd_variant != 1 && g_fwd_variant != 3), DLA_E_UNSUPP,
+              "attn_fwd: packed rows (seg_start) need causal attention and the ping-pong forward kernel");
   DLA_REQUIRE(D == 64 || D == 128, DLA_E_UNSUPP, "attn_fwd: head_dim %d not supported (64 or 128)", D);
   DLA_REQUIRE(Hq % Hk == 0 && B > 0 && T > 0, DLA_E_BADARG, "attn_fwd: bad shape B=%d T=%d Hq=%d Hk=%d", B, T, Hq, Hk);
   DLA_REQUIRE(o_st % 8 == 0 && o_sh % 8 == 0 && o_sb % 8 == 0, DLA_E_BADARG, "attn_fwd: output strides must be multiples of 8");
@@ -681,6 +704,7 @@ int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* ls
   if ((rc = make_qkv_map(&tmV, v, B, T, Hk, D, kv_sb, kv_st, kv_sh))) return rc;
   Params p{};
   p.B = B; p.T = T; p.Hq = Hq; p.Hk = Hk; p.D = D; p.scale = scale; p.causal = causal; p.seqlens = seqlens;
+  p.seg_start = seg_start;
   p.o = (bf16*)o; p.o_sb = o_sb; p.o_st = o_st; p.o_sh = o_sh; p.lse = lse;
   dim3 grid((T + BQ - 1) / BQ, Hq, B);
   cudaStream_t s = (cudaStream_t)stream;
@@ -704,7 +728,16 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
                  void* dk, void* dv, float* dq_acc, float* delta, int B, int T, int Hq, int Hk, int D, int64_t q_sb,
                  int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh, int64_t o_sb, int64_t o_st,
                  int64_t o_sh, const int32_t* seqlens, float scale, int causal, void* stream) {
+  return dla_attn_bwd_seg(q, k, v, o, dout, lse, dq, dk, dv, dq_acc, delta, B, T, Hq, Hk, D, q_sb, q_st, q_sh, kv_sb, kv_st, kv_sh,
+                          o_sb, o_st, o_sh, seqlens, nullptr, scale, causal, stream);
+}
+
+int dla_attn_bwd_seg(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse, void* dq,
+                     void* dk, void* dv, float* dq_acc, float* delta, int B, int T, int Hq, int Hk, int D, int64_t q_sb,
+                     int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh, int64_t o_sb, int64_t o_st,
+                     int64_t o_sh, const int32_t* seqlens, const int32_t* seg_start, float scale, int causal, void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(seg_start == nullptr || causal, DLA_E_UNSUPP, "attn_bwd: packed rows (seg_start) need causal attention");
   DLA_REQUIRE(D == 64 || D == 128, DLA_E_UNSUPP, "attn_bwd: head_dim %d not supported (64 or 128)", D);
   DLA_REQUIRE(Hq % Hk == 0 && B > 0 && T > 0, DLA_E_BADARG, "attn_bwd: bad shape");
   CUtensorMap tmQ, tmK, tmV, tmdO;
@@ -727,6 +760,7 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   if ((rc = check_launch("attn_bwd.prep"))) return rc;
   Params p{};
   p.B = B; p.T = T; p.Hq = Hq; p.Hk = Hk; p.D = D; p.scale = scale; p.causal = causal; p.seqlens = seqlens;
+  p.seg_start = seg_start;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_acc = dq_acc;
   // contract: dq has q's strides, dk/dv have k/v's strides
   p.dk = (bf16*)dk; p.dv = (bf16*)dv; p.dkv_sb = kv_sb; p.dkv_st = kv_st; p.dkv_sh = kv_sh;

@@ -16,6 +16,9 @@ struct Params {
   float scale;
   int causal;
   const int32_t* seqlens;
+  // packed sequences (several documents per row): seg_start[b, t] = index of the first token of t's document, so the
+  // keys a query may see are [seg_start[q], q].  Non-decreasing along t; nullptr = one document per row.
+  const int32_t* seg_start;
   // forward
   bf16* o;
   int64_t o_sb, o_st, o_sh;

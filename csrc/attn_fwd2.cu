@@ -64,13 +64,18 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
   int len = p.T;
   if (p.seqlens != nullptr) len = min(len, p.seqlens[b]);
   const int n_all = (len + 127) >> 7;
+  // packed rows: kv tiles that end before the document of the pair's FIRST query row starts are skipped for both
+  // tiles (seg_start is non-decreasing, so that row has the smallest start); all loop counters below are relative
+  // to that first tile `jb`
+  int jb = 0;
+  if (p.seg_start != nullptr && pi * 256 < len) jb = p.seg_start[(int64_t)b * p.T + pi * 256] >> 7;
   int nX[2];
 #pragma unroll
   for (int x = 0; x < 2; ++x) {
     const int t = 2 * pi + x;
     int n = p.causal ? min(n_all, t + 1) : n_all;
     if (t * 128 >= len) n = 0;
-    nX[x] = n;
+    nX[x] = max(n - jb, 0);
   }
   const int n = max(nX[0], nX[1]);
 
@@ -111,11 +116,11 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         tc::mbar_wait(&k_empty[st], ph);
         tc::mbar_expect_tx(&k_full[st], TILE_BYTES);
 #pragma unroll
-        for (int c = 0; c < NB; ++c) tc::tma_load_4d(sK + st * TILE_BYTES + c * 16384, &tmK, &k_full[st], c * 64, hk, j * 128, b);
+        for (int c = 0; c < NB; ++c) tc::tma_load_4d(sK + st * TILE_BYTES + c * 16384, &tmK, &k_full[st], c * 64, hk, (jb + j) * 128, b);
         tc::mbar_wait(&v_empty[st], ph);
         tc::mbar_expect_tx(&v_full[st], TILE_BYTES);
 #pragma unroll
-        for (int c = 0; c < NB; ++c) tc::tma_load_4d(sV + st * TILE_BYTES + c * 16384, &tmV, &v_full[st], c * 64, hk, j * 128, b);
+        for (int c = 0; c < NB; ++c) tc::tma_load_4d(sV + st * TILE_BYTES + c * 16384, &tmV, &v_full[st], c * 64, hk, (jb + j) * 128, b);
       }
     }
   } else if (warp == 1) {
@@ -178,17 +183,22 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     const uint32_t tO = tmem_base + lane_off + 256 + x * 128;
     const float scale2 = p.scale * kLog2e;
     float m_ref = -INFINITY, l_run = 0.f;
+    // first key this row may see (start of its document when rows are packed)
+    const int row_lo = (p.seg_start != nullptr && q_idx < len) ? p.seg_start[(int64_t)b * p.T + q_idx] : 0;
+    // the last row of the tile has the largest start: below it, some row of the tile needs the lower mask
+    const int tile_lo = (p.seg_start != nullptr) ? p.seg_start[(int64_t)b * p.T + min(q0 + 127, max(len - 1, 0))] : 0;
 
     for (int j = 0; j < nt; ++j) {
-      const int kv0 = j * 128;
+      const int kv0 = (jb + j) * 128;
       tc::mbar_wait(&s_full[x], j & 1);
       tc::tc_fence_after();
-      const bool need_mask = (p.causal && kv0 + 127 > q0) || (kv0 + 128 > len);
-      int limit = 128;                            // valid columns of this row in this tile
+      const bool need_mask = (p.causal && kv0 + 127 > q0) || (kv0 + 128 > len) || (kv0 < tile_lo);
+      int limit = 128, lo = 0;                    // valid columns of this row in this tile: [lo, limit)
       if (need_mask) {
         int lim = len;
         if (p.causal) lim = min(lim, q_idx + 1);
         limit = lim - kv0;
+        lo = row_lo - kv0;
       }
       // ---- pass 1: row maximum.  The four 32-column loads are in flight together (one wait), and four
       // independent max chains keep the FMNMX latency off the critical path of this lone warp.
@@ -204,7 +214,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(v[i]));
         } else {
 #pragma unroll
-          for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], i < limit ? __uint_as_float(v[i]) : -INFINITY);
+          for (int i = 0; i < 128; ++i) m4[i & 3] = fmaxf(m4[i & 3], (i < limit && i >= lo) ? __uint_as_float(v[i]) : -INFINITY);
         }
         mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
       }
@@ -251,8 +261,8 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
             for (int i = 0; i < 64; i += 2) {
               const int c = half * 64 + i;
-              const float p0 = c < limit ? ex2_approx(fmaf(__uint_as_float(v[c]), scale2, neg_m)) : 0.f;
-              const float p1 = c + 1 < limit ? ex2_approx(fmaf(__uint_as_float(v[c + 1]), scale2, neg_m)) : 0.f;
+              const float p0 = (c < limit && c >= lo) ? ex2_approx(fmaf(__uint_as_float(v[c]), scale2, neg_m)) : 0.f;
+              const float p1 = (c + 1 < limit && c + 1 >= lo) ? ex2_approx(fmaf(__uint_as_float(v[c + 1]), scale2, neg_m)) : 0.f;
               s4[(i >> 1) & 3] += p0 + p1;
               pk[i >> 1] = pack_bf16x2(p0, p1);
             }

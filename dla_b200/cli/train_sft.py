@@ -47,10 +47,9 @@ def main() -> None:
     data_cfg.setdefault("max_seq_length", mc.get("max_seq_length", 2048))
     max_len = int(data_cfg.get("max_length") or data_cfg["max_seq_length"])
     train_ds = build_instruction_dataset(data_cfg, bundle.tokenizer, split="train")
-    collate = PackedCollator(max_len, train_ds.pad_id) if data_cfg.get("packing") and data_cfg.get("honor_packing", True) \
-        and ctx.device.type != "cuda" else None
-    # NOTE: packed (segment-masked) attention currently runs on the reference path only; on CUDA the flag
-    # keeps right-padded batches so the flash kernel is used.
+    # ``data.packing: true`` (R/config/sft_config.yaml:16): several documents per row; the flash kernels mask (and skip
+    # tiles) by document through ``segment_ids``, positions restart per document (``position_ids``)
+    collate = PackedCollator(max_len, train_ds.pad_id) if data_cfg.get("packing") and data_cfg.get("honor_packing", True) else None
     loader, sampler = build_loader(train_ds, int(oc["micro_batch_size"]), ctx.world_size, ctx.rank, shuffle=True,
                                    num_workers=int(data_cfg.get("num_workers", 4)), seed=seed, collate_fn=collate)
     eval_loader = None

@@ -480,26 +480,36 @@ def embedding(ids: torch.Tensor, table: torch.Tensor, pos_table: Optional[torch.
 # attention
 # =======================================================================================
 
+def segment_starts(segment_ids: torch.Tensor) -> torch.Tensor:
+    """``[B, T]`` int32: for every token the index of the first token of its document (``segment_ids`` as produced by
+    ``PackedCollator``: consecutive equal ids form a document, 0 = padding at the end of the row).  This is the form
+    the flash kernels take: the keys a query may see are ``[start[q], q]``."""
+    B, T = segment_ids.shape
+    idx = torch.arange(T, device=segment_ids.device, dtype=torch.int32).expand(B, T)
+    first = torch.ones(B, T, dtype=torch.bool, device=segment_ids.device)
+    first[:, 1:] = segment_ids[:, 1:] != segment_ids[:, :-1]
+    return torch.cummax(torch.where(first, idx, torch.zeros_like(idx)), dim=1).values.to(torch.int32).contiguous()
+
+
 class _Attention(Function):
     @staticmethod
-    def forward(ctx, q, k, v, seqlens, causal, scale):
+    def forward(ctx, q, k, v, seqlens, causal, scale, seg_start=None):
         B, T, Hq, D = q.shape
         Hk = k.shape[2]
         o = torch.empty(B, T, Hq, D, dtype=q.dtype, device=q.device)
         lse = torch.empty(B, Hq, T, dtype=torch.float32, device=q.device)
-        N.call("dla_attn_fwd", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(lse), B, T, Hq, Hk, D,
+        N.call("dla_attn_fwd_seg", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(lse), B, T, Hq, Hk, D,
                q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
-               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), scale, int(causal), _s(q))
-        ctx.save_for_backward(q, k, v, o, lse, seqlens) if seqlens is not None else ctx.save_for_backward(q, k, v, o, lse)
-        ctx.has_len = seqlens is not None
+               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), N.ptr(seg_start), scale, int(causal), _s(q))
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.seqlens, ctx.seg_start = seqlens, seg_start
         ctx.meta = (causal, scale)
         return o
 
     @staticmethod
     def backward(ctx, do):
-        saved = ctx.saved_tensors
-        q, k, v, o, lse = saved[:5]
-        seqlens = saved[5] if ctx.has_len else None
+        q, k, v, o, lse = ctx.saved_tensors
+        seqlens, seg_start = ctx.seqlens, ctx.seg_start
         causal, scale = ctx.meta
         B, T, Hq, D = q.shape
         Hk = k.shape[2]
@@ -518,11 +528,11 @@ class _Attention(Function):
         dq_acc = torch.empty(B, T, Hq, D, dtype=torch.float32, device=q.device)
         delta = torch.empty(B, Hq, T, dtype=torch.float32, device=q.device)
         assert do.stride(2) == o.stride(2) and do.stride(1) == o.stride(1) and do.stride(0) == o.stride(0)
-        N.call("dla_attn_bwd", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
+        N.call("dla_attn_bwd_seg", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
                N.ptr(dq), N.ptr(dk), N.ptr(dv), N.ptr(dq_acc), N.ptr(delta), B, T, Hq, Hk, D,
                q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
-               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), scale, int(causal), _s(q))
-        return dq, dk, dv, None, None, None
+               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), N.ptr(seg_start), scale, int(causal), _s(q))
+        return dq, dk, dv, None, None, None, None
 
 
 class _AttentionPacked(Function):
@@ -532,24 +542,23 @@ class _AttentionPacked(Function):
     Llama-3-8B layer)."""
 
     @staticmethod
-    def forward(ctx, qkv, n_q, n_kv, seqlens, causal, scale):
+    def forward(ctx, qkv, n_q, n_kv, seqlens, causal, scale, seg_start=None):
         B, T, _, D = qkv.shape
         q, k, v = qkv[:, :, :n_q], qkv[:, :, n_q:n_q + n_kv], qkv[:, :, n_q + n_kv:]
         o = torch.empty(B, T, n_q, D, dtype=qkv.dtype, device=qkv.device)
         lse = torch.empty(B, n_q, T, dtype=torch.float32, device=qkv.device)
-        N.call("dla_attn_fwd", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(lse), B, T, n_q, n_kv, D,
+        N.call("dla_attn_fwd_seg", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(lse), B, T, n_q, n_kv, D,
                q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
-               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), scale, int(causal), _s(qkv))
-        ctx.save_for_backward(qkv, o, lse, seqlens) if seqlens is not None else ctx.save_for_backward(qkv, o, lse)
-        ctx.has_len = seqlens is not None
+               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), N.ptr(seg_start), scale, int(causal), _s(qkv))
+        ctx.save_for_backward(qkv, o, lse)
+        ctx.seqlens, ctx.seg_start = seqlens, seg_start
         ctx.meta = (n_q, n_kv, causal, scale)
         return o
 
     @staticmethod
     def backward(ctx, do):
-        saved = ctx.saved_tensors
-        qkv, o, lse = saved[:3]
-        seqlens = saved[3] if ctx.has_len else None
+        qkv, o, lse = ctx.saved_tensors
+        seqlens, seg_start = ctx.seqlens, ctx.seg_start
         n_q, n_kv, causal, scale = ctx.meta
         B, T, _, D = qkv.shape
         q, k, v = qkv[:, :, :n_q], qkv[:, :, n_q:n_q + n_kv], qkv[:, :, n_q + n_kv:]
@@ -558,24 +567,27 @@ class _AttentionPacked(Function):
         dq, dk, dv = dqkv[:, :, :n_q], dqkv[:, :, n_q:n_q + n_kv], dqkv[:, :, n_q + n_kv:]
         dq_acc = torch.empty(B, T, n_q, D, dtype=torch.float32, device=qkv.device)
         delta = torch.empty(B, n_q, T, dtype=torch.float32, device=qkv.device)
-        N.call("dla_attn_bwd", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
+        N.call("dla_attn_bwd_seg", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
                N.ptr(dq), N.ptr(dk), N.ptr(dv), N.ptr(dq_acc), N.ptr(delta), B, T, n_q, n_kv, D,
                q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
-               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), scale, int(causal), _s(qkv))
-        return dqkv, None, None, None, None, None
+               o.stride(0), o.stride(1), o.stride(2), N.ptr(seqlens), N.ptr(seg_start), scale, int(causal), _s(qkv))
+        return dqkv, None, None, None, None, None, None
 
 
 def attention_qkv(qkv: torch.Tensor, n_q: int, n_kv: int, seqlens: Optional[torch.Tensor] = None, causal: bool = True,
                   scale: Optional[float] = None, segment_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Causal GQA attention on a packed, contiguous ``[B, T, n_q + 2 n_kv, D]`` projection; returns ``[B, T, n_q, D]``."""
-    if not qkv.is_cuda or segment_ids is not None or not qkv.is_contiguous():
+    if not qkv.is_cuda or not qkv.is_contiguous() or (segment_ids is not None and not causal):
         return attention(qkv[:, :, :n_q], qkv[:, :, n_q:n_q + n_kv], qkv[:, :, n_q + n_kv:], seqlens=seqlens, causal=causal,
                          scale=scale, segment_ids=segment_ids)
     scale = scale if scale is not None else 1.0 / math.sqrt(qkv.shape[-1])
     _check_bf16(qkv)
     if seqlens is not None:
         seqlens = seqlens.to(torch.int32)
-    return _AttentionPacked.apply(qkv, n_q, n_kv, seqlens, causal, scale)
+    seg_start = _seg_start_arg(segment_ids, seqlens, qkv.shape[1])
+    if seg_start is not None and seqlens is None:
+        seqlens = (segment_ids > 0).sum(1).to(torch.int32)
+    return _AttentionPacked.apply(qkv, n_q, n_kv, seqlens, causal, scale, seg_start)
 
 
 def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, seqlens: Optional[torch.Tensor] = None,
@@ -584,12 +596,32 @@ def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, seqlens: Option
     """Causal GQA attention on ``[B, T, H, D]`` tensors (views of a packed QKV are fine: strides are
     passed through).  ``seqlens [B]`` int32 masks right padding."""
     scale = scale if scale is not None else 1.0 / math.sqrt(q.shape[-1])
-    if not q.is_cuda or segment_ids is not None:
+    if not q.is_cuda or (segment_ids is not None and not causal):
         return R.attention(q, k, v, causal=causal, seqlens=seqlens, scale=scale, segment_ids=segment_ids)
     _check_bf16(q, k, v)
     if seqlens is not None:
         seqlens = seqlens.to(torch.int32)
-    return _Attention.apply(q, k, v, seqlens, causal, scale)
+    seg_start = _seg_start_arg(segment_ids, seqlens, q.shape[1])
+    if seg_start is not None and seqlens is None:
+        seqlens = (segment_ids > 0).sum(1).to(torch.int32)
+    return _Attention.apply(q, k, v, seqlens, causal, scale, seg_start)
+
+
+_SEG_CACHE: dict = {}
+
+
+def _seg_start_arg(segment_ids: Optional[torch.Tensor], seqlens: Optional[torch.Tensor], T: int) -> Optional[torch.Tensor]:
+    """The kernels' ``seg_start`` for a batch of packed rows; computed once per batch tensor (every layer of a forward
+    and of its recomputation passes the same ``segment_ids`` object)."""
+    if segment_ids is None:
+        return None
+    key = (segment_ids.data_ptr(), segment_ids._version, tuple(segment_ids.shape))
+    hit = _SEG_CACHE.get("k")
+    if hit is not None and hit[0] == key and hit[1] is segment_ids:
+        return hit[2]
+    ss = segment_starts(segment_ids)
+    _SEG_CACHE["k"] = (key, segment_ids, ss)
+    return ss
 
 
 # =======================================================================================

@@ -48,6 +48,8 @@ _SIGNATURES = {
     "dla_logprob_grad_inplace": [P, P, P, P, I, I, I64, P],
     "dla_attn_fwd": [P, P, P, P, P, I, I, I, I, I] + [I64] * 9 + [P, F, I, P],
     "dla_attn_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I] + [I64] * 9 + [P, F, I, P],
+    "dla_attn_fwd_seg": [P, P, P, P, P, I, I, I, I, I] + [I64] * 9 + [P, P, F, I, P],
+    "dla_attn_bwd_seg": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I] + [I64] * 9 + [P, P, F, I, P],
     "dla_attn_decode": [P, P, P, P, P, I, I, I, I, I, F, P],
     "dla_gemm_skinny_bf16": [P, P, P, P, P, I, I, I, I64, I64, I64, I64, I, I, P],
     "dla_decode_attn_fused": [P, I64, P, P, P, P, P, P, I, I, I, I, I, I, F, P],

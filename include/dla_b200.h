@@ -192,6 +192,21 @@ int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
                  int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
                  int64_t o_sb, int64_t o_st, int64_t o_sh,
                  const int32_t* seqlens, float scale, int causal, void* stream);
+/* Packed rows (several documents per row, `data.packing: true` of R/config/sft_config.yaml:16): as dla_attn_fwd /
+ * dla_attn_bwd with seg_start (nullable int32 [B,T], contiguous): seg_start[b,t] = index of the first token of t's
+ * document, non-decreasing along t.  A query sees the keys [seg_start[q], q]; kv tiles (forward) and query tiles
+ * (backward) that lie entirely outside that range are skipped, not just masked.  Causal only. */
+int dla_attn_fwd_seg(const void* q, const void* k, const void* v, void* o, float* lse,
+                     int B, int T, int Hq, int Hk, int D,
+                     int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
+                     int64_t o_sb, int64_t o_st, int64_t o_sh,
+                     const int32_t* seqlens, const int32_t* seg_start, float scale, int causal, void* stream);
+int dla_attn_bwd_seg(const void* q, const void* k, const void* v, const void* o, const void* dout,
+                     const float* lse, void* dq, void* dk, void* dv, float* dq_acc, float* delta,
+                     int B, int T, int Hq, int Hk, int D,
+                     int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
+                     int64_t o_sb, int64_t o_st, int64_t o_sh,
+                     const int32_t* seqlens, const int32_t* seg_start, float scale, int causal, void* stream);
 /* Single-token decode attention over a contiguous KV cache [B, S_max, Hk, D] with per-row lengths. */
 int dla_attn_decode(const void* q, const void* kcache, const void* vcache, void* o,
                     const int32_t* lens, int B, int S_max, int Hq, int Hk, int D, float scale,

@@ -50,6 +50,26 @@ def _log(d: Path, phase: str, **kw):
     return base
 
 
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("device", ["cpu", pytest.param("cuda", marks=pytest.mark.gpu)])
+def test_sft_with_sequence_packing(work, device):
+    """``data.packing: true`` (R/config/sft_config.yaml:16) packs several documents per row; on CUDA the flash kernels
+    take the document boundaries, so the flag no longer falls back to padded rows there."""
+    _DEVICE[0] = device
+    d = work / f"pack_{device}"
+    d.mkdir(exist_ok=True)
+    cfg = _write(d / "sft_pack.yaml", {
+        "seed": 1, "model": {"model_name_or_path": "tiny-llama", "max_seq_length": 160},
+        "data": {"source": "local", "train_path": str(work / "sft.jsonl"), "num_workers": 0, "packing": True},
+        "optimization": {"micro_batch_size": 6, "learning_rate": 1e-3, "warmup_steps": 1, "max_train_steps": 3},
+        "logging": _log(d, "sft_pack", save_every_steps=0), "hardware": {"device": device}})
+    out = _run("dla_b200.cli.train_sft", "--config", cfg)
+    assert "Training complete" in out
+    metrics = [json.loads(l) for l in (d / "logs" / "sft_pack" / "metrics.jsonl").read_text().splitlines()]
+    losses = [m["train/loss"] for m in metrics if "train/loss" in m]
+    assert losses and all(l == l and l < 20 for l in losses)
+
+
 @pytest.mark.timeout(1500)
 @pytest.mark.parametrize("device", ["cpu", pytest.param("cuda", marks=pytest.mark.gpu)])
 def test_phase_chain(work, device):

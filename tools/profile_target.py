@@ -47,5 +47,30 @@ elif what == "lmhead":
     lab = torch.randint(0, 128256, (4096,), device=dev)
     for _ in range(2):
         F.linear_logprob(h, w, lab)
+elif what == "rmsnorm":
+    x, d, w = r(8192, 4096).requires_grad_(), r(8192, 4096).requires_grad_(), torch.ones(4096, device=dev, dtype=torch.bfloat16).requires_grad_()
+    for _ in range(3):
+        xn, h = F.add_rmsnorm(x.view(8, 1024, 4096), d.view(8, 1024, 4096), w, 1e-5)
+        torch.autograd.grad([xn, h], [x, d], [torch.ones_like(xn), torch.ones_like(h)])
+elif what == "rope":
+    qkv = r(8192, 48 * 128)
+    pos = torch.arange(1024, device=dev, dtype=torch.int32).repeat(8)
+    for _ in range(3):
+        F.rope_qkv(qkv, pos, 32, 8, 128, 500000.0, None, max_pos=8192)
+elif what == "swiglu":
+    gu = r(8192, 28672).requires_grad_()
+    for _ in range(3):
+        y = F.swiglu(gu)
+        torch.autograd.grad(y, gu, torch.ones_like(y))
+elif what == "adamw":
+    from dla_b200.ops import native as N
+    n = 218_112_000
+    master, m, v = (torch.zeros(n, device=dev) for _ in range(3))
+    g = torch.zeros(n, device=dev, dtype=torch.bfloat16)
+    prm = torch.empty(n, device=dev, dtype=torch.bfloat16)
+    coef = torch.ones(1, device=dev)
+    for _ in range(3):
+        N.call("dla_adamw", N.ptr(master), N.ptr(m), N.ptr(v), N.ptr(g), N.ptr(prm), n, 1e-5, 0.9, 0.999, 1e-8, 0.01, 0.1, 0.001,
+               N.ptr(coef), 1.0, 0, N.stream_ptr())
 torch.cuda.synchronize()
 print("ok", what)
