@@ -296,9 +296,10 @@ __global__ void attn_bwd_prep_kernel(const bf16* __restrict__ o, const bf16* __r
 }
 
 __global__ void attn_bwd_dq_cast_kernel(const float* __restrict__ dq_acc, bf16* __restrict__ dq, int64_t rows, int D,
-                                        int Hq, int T, int64_t sb, int64_t st, int64_t sh) {
+                                        int Hq, int T, int64_t sb, int64_t st, int64_t sh, int tiled) {
   const int per_row = D >> 3;
   const int64_t total = rows * per_row;
+  const int nT = (T + 127) >> 7;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int64_t row = idx / per_row;
     const int c = (int)(idx % per_row) * 8;
@@ -307,8 +308,17 @@ __global__ void attn_bwd_dq_cast_kernel(const float* __restrict__ dq_acc, bf16* 
     const int t = (int)(bt % T);
     const int64_t b = bt / T;
     float f[8];
-    *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(dq_acc + row * D + c);
-    *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(dq_acc + row * D + c + 4);
+    if (!tiled) {
+      *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(dq_acc + row * D + c);
+      *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(dq_acc + row * D + c + 4);
+    } else {
+      // [b, h, t / 128, c / 32] blocks of [128 rows x 32 fp32]; inside a block the eight 16-byte chunks of a row are
+      // XOR-swizzled with the row index (the shared-memory staging image of attn_bwd2_kernel)
+      const int r = t & 127, blk = c >> 5, ch = (c & 31) >> 2;
+      const float* base = dq_acc + ((((b * Hq + h) * nT + (t >> 7)) * (D >> 5) + blk) * 128 + r) * 32;
+      *reinterpret_cast<float4*>(f) = *reinterpret_cast<const float4*>(base + ((ch ^ (r & 7)) << 2));
+      *reinterpret_cast<float4*>(f + 4) = *reinterpret_cast<const float4*>(base + (((ch + 1) ^ (r & 7)) << 2));
+    }
     st8(dq + b * sb + t * st + h * sh + c, pack8(f));
   }
 }
@@ -672,11 +682,19 @@ using namespace dla;
 using namespace dla::attn;
 
 static int g_fwd_variant = 0;     // 0 = auto (ping-pong kernel), 1 = first-generation kernel, 2 = ping-pong kernel
+// 0 = auto: the pipelined kernel (attn_bwd2.cu) from T = 2048 on, the first-generation kernel below (measured on B200,
+// 32/8 heads, D = 128: 307 vs 335 us at B=8 T=1024, 1006 vs 913 us at B=2 T=4096); 1 = first generation; 2 = pipelined
+static int g_bwd_variant = 0;
 
 extern "C" {
 
 int dla_attn_set_fwd_variant(int v) {
   g_fwd_variant = v;
+  return 0;
+}
+
+int dla_attn_set_bwd_variant(int v) {
+  g_bwd_variant = v;
   return 0;
 }
 
@@ -765,7 +783,18 @@ int dla_attn_bwd_seg(const void* q, const void* k, const void* v, const void* o,
   // contract: dq has q's strides, dk/dv have k/v's strides
   p.dk = (bf16*)dk; p.dv = (bf16*)dv; p.dkv_sb = kv_sb; p.dkv_st = kv_st; p.dkv_sh = kv_sh;
   dim3 grid((unsigned)(((T + BKV - 1) / BKV) * Hk * B));
-  if (D == 128) {
+  p.debug_flags = g_bwd_variant >= 16 ? (g_bwd_variant & 15) : 0;
+  const bool gen2 = (g_bwd_variant >= 2 || (g_bwd_variant == 0 && T >= 2048)) && T < 65536;
+  p.dq_tiled = gen2 ? 1 : 0;
+  if (gen2 && T % BQ != 0) {
+    // the padded rows of each (batch, head)'s last query tile are part of the tiled accumulator: the pre-pass zeroed
+    // only the first B*T*Hq*D floats, clear the rest
+    const int64_t have = rows * D, need = (int64_t)B * Hq * ((T + BQ - 1) / BQ) * BQ * D;
+    DLA_CUDA(cudaMemsetAsync(dq_acc + have, 0, (size_t)(need - have) * sizeof(float), s));
+  }
+  if (gen2) {
+    if ((rc = attn_bwd2_dispatch(tmQ, tmK, tmV, tmdO, tmdQ, p, s))) return rc;
+  } else if (D == 128) {
     constexpr int smem = 4 * 128 * 128 * 2 + 2 * 128 * 128 * 2 + 1024 + 256;
     static bool set = false;
     if (!set) { DLA_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); set = true; }
@@ -779,7 +808,7 @@ int dla_attn_bwd_seg(const void* q, const void* k, const void* v, const void* o,
   if ((rc = check_launch("attn_bwd"))) return rc;
   int64_t blocks = (rows * (D / 8) + 255) / 256;
   if (blocks > (int64_t)kNumSMs * 16) blocks = (int64_t)kNumSMs * 16;
-  attn_bwd_dq_cast_kernel<<<(unsigned)blocks, 256, 0, s>>>(dq_acc, (bf16*)dq, rows, D, Hq, T, q_sb, q_st, q_sh);
+  attn_bwd_dq_cast_kernel<<<(unsigned)blocks, 256, 0, s>>>(dq_acc, (bf16*)dq, rows, D, Hq, T, q_sb, q_st, q_sh, p.dq_tiled);
   return check_launch("attn_bwd.dq_cast");
 }
 

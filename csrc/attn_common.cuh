@@ -19,6 +19,8 @@ struct Params {
   // packed sequences (several documents per row): seg_start[b, t] = index of the first token of t's document, so the
   // keys a query may see are [seg_start[q], q].  Non-decreasing along t; nullptr = one document per row.
   const int32_t* seg_start;
+  int dq_tiled;      // dq_acc holds [B, Hq, ceil(T/128), HD/32] blocks of [128 rows x 32 fp32] in the swizzled staging image
+  int debug_flags;   // timing experiments only (dla_attn_set_bwd_variant >= 16): bit 0 = skip the dQ reduce-add
   // forward
   bf16* o;
   int64_t o_sb, o_st, o_sh;
@@ -52,6 +54,9 @@ inline int make_qkv_map(CUtensorMap* m, const void* base, int B, int T, int H, i
 
 // attn_fwd2.cu
 int attn_fwd2_dispatch(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t s);
+// attn_bwd2.cu: pipelined backward (transposed score tiles, P^T / dS^T consumed from TMEM)
+int attn_bwd2_dispatch(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV, const CUtensorMap& tmdO,
+                       const CUtensorMap& tmdQ, const Params& p, cudaStream_t s);
 // attn_fwd3.cu
 int attn_fwd3_dispatch(const CUtensorMap& tmQ, const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t s);
 

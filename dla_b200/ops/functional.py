@@ -525,7 +525,7 @@ class _Attention(Function):
         else:
             q, k, v = _c(q), _c(k), _c(v)
             dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        dq_acc = torch.empty(B, T, Hq, D, dtype=torch.float32, device=q.device)
+        dq_acc = torch.empty(B * Hq * (-(-T // 128) * 128) * D, dtype=torch.float32, device=q.device)   # padded to whole query tiles
         delta = torch.empty(B, Hq, T, dtype=torch.float32, device=q.device)
         assert do.stride(2) == o.stride(2) and do.stride(1) == o.stride(1) and do.stride(0) == o.stride(0)
         N.call("dla_attn_bwd_seg", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
@@ -565,7 +565,7 @@ class _AttentionPacked(Function):
         do = _c(do)
         dqkv = torch.empty_like(qkv)
         dq, dk, dv = dqkv[:, :, :n_q], dqkv[:, :, n_q:n_q + n_kv], dqkv[:, :, n_q + n_kv:]
-        dq_acc = torch.empty(B, T, n_q, D, dtype=torch.float32, device=qkv.device)
+        dq_acc = torch.empty(B * n_q * (-(-T // 128) * 128) * D, dtype=torch.float32, device=qkv.device)  # padded to whole query tiles
         delta = torch.empty(B, n_q, T, dtype=torch.float32, device=qkv.device)
         N.call("dla_attn_bwd_seg", N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(o), N.ptr(do), N.ptr(lse),
                N.ptr(dq), N.ptr(dk), N.ptr(dv), N.ptr(dq_acc), N.ptr(delta), B, T, n_q, n_kv, D,

@@ -60,6 +60,7 @@ _SIGNATURES = {
     "dla_gae": [P, P, P, P, P, I, I, F, F, I, P],
     "dla_distill_kl": [P, I64, P, P, I, P, I, I, F, P, P, I64, P],
     "dla_attn_set_fwd_variant": [I],
+    "dla_attn_set_bwd_variant": [I],
     "dla_peer_allgather_small": [P, P, I, I, P, I, I, c_uint32, I, P, P],
     "dla_sample_top_p": [P, I, I, I, I64, F, F, c_uint64, c_uint64, P, P, P],
     "dla_fused_rs_adamw": [P, P, I, I, I64, I64, F, P, P, P, P, P, F, F, F, F, F, F, F, P, I, P],

@@ -179,12 +179,15 @@ int dla_lmhead_logprob_noalloc_max_vocab(void);
  * one-tile kernel (csrc/attention.cu), 2 = ping-pong, 3 = ping-pong with early S release / P through shared memory
  * (csrc/attn_fwd3.cu; measured slower, experimental).  Process-wide; for benchmarks and A/B tests. */
 int dla_attn_set_fwd_variant(int v);
+/* Backward kernel choice: 0 = auto (pipelined kernel with transposed score tiles, csrc/attn_bwd2.cu, from T = 2048 on;
+ * first-generation serial kernel, csrc/attention.cu, below), 1 = first generation, 2 = pipelined. */
+int dla_attn_set_bwd_variant(int v);
 int dla_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse,
                  int B, int T, int Hq, int Hk, int D,
                  int64_t q_sb, int64_t q_st, int64_t q_sh, int64_t kv_sb, int64_t kv_st, int64_t kv_sh,
                  int64_t o_sb, int64_t o_st, int64_t o_sh,
                  const int32_t* seqlens, float scale, int causal, void* stream);
-/* Backward. dq_acc: fp32 scratch [B,T,Hq,D] (zeroed inside); delta: fp32 scratch [B,Hq,T].
+/* Backward. dq_acc: fp32 scratch of B * Hq * ceil(T/128)*128 * D elements (zeroed inside); delta: fp32 scratch [B,Hq,T].
  * dq must have q's strides, dk/dv must have k/v's strides; dout must have o's strides. */
 int dla_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout,
                  const float* lse, void* dq, void* dk, void* dv, float* dq_acc, float* delta,

@@ -333,6 +333,33 @@ def test_attention_fwd_early_s_variant(native_lib, B, T, Hq, Hk, D, ragged):
     _close(o, o2, rtol=1e-2, atol=1e-2, what="fwd3 vs fwd2")
 
 
+@pytest.mark.parametrize("B,T,Hq,Hk,D,ragged", ATTN_CASES)
+def test_attention_bwd_both_generations_agree(native_lib, B, T, Hq, Hk, D, ragged):
+    """The serial first-generation backward (variant 1, default below T = 2048) and the pipelined kernel with transposed
+    score tiles (variant 2, default from T = 2048) produce the same gradients."""
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(14)
+    qkv = _rand(B, T, Hq + 2 * Hk, D)
+    seqlens = torch.randint(max(1, T // 3), T + 1, (B,), device=DEV, dtype=torch.int32) if ragged else None
+    g = _rand(B, T, Hq, D)
+    if seqlens is not None:
+        g = g * (torch.arange(T, device=DEV)[None, :] < seqlens[:, None])[:, :, None, None]
+    grads = []
+    for variant in (1, 2):
+        N.call("dla_attn_set_bwd_variant", variant)
+        try:
+            x = qkv.clone().requires_grad_()
+            F.attention_qkv(x, Hq, Hk, seqlens=seqlens, causal=True).backward(g)
+            torch.cuda.synchronize()
+        finally:
+            N.call("dla_attn_set_bwd_variant", 0)
+        grads.append(x.grad.float())
+    valid = torch.ones(B, T, 1, 1, device=DEV, dtype=torch.bool) if seqlens is None else \
+        (torch.arange(T, device=DEV)[None, :] < seqlens[:, None])[:, :, None, None]
+    _rel(grads[0] * valid, grads[1] * valid, 1e-2, what="bwd gen1 vs gen2")
+
+
 def _packed_segments(B, T, seed, device):
     """Random packed rows: documents of random lengths back to back, padding (segment 0) at the end of some rows."""
     g = torch.Generator().manual_seed(seed)
@@ -348,10 +375,21 @@ def _packed_segments(B, T, seed, device):
 
 
 @pytest.mark.parametrize("B,T,Hq,Hk,D", [(2, 512, 4, 2, 128), (3, 1000, 8, 2, 128), (2, 384, 4, 4, 64), (1, 2048, 4, 1, 128)])
-def test_attention_packed_rows_fwd_bwd(native_lib, B, T, Hq, Hk, D):
+@pytest.mark.parametrize("bwd_variant", [1, 2])
+def test_attention_packed_rows_fwd_bwd(native_lib, B, T, Hq, Hk, D, bwd_variant):
     """``data.packing``: several documents per row.  The flash kernels take the per-token document start and must
     equal the fp32 reference with the (same segment) x (causal) mask, forward and backward, including rows whose
     documents straddle 128-token tile boundaries and padded tails."""
+    from dla_b200.ops import native as N
+
+    N.call("dla_attn_set_bwd_variant", bwd_variant)
+    try:
+        _packed_case(B, T, Hq, Hk, D)
+    finally:
+        N.call("dla_attn_set_bwd_variant", 0)
+
+
+def _packed_case(B, T, Hq, Hk, D):
     torch.manual_seed(21)
     seg = _packed_segments(B, T, 5, DEV)
     qkv = _rand(B, T, Hq + 2 * Hk, D)

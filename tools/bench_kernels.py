@@ -126,11 +126,36 @@ def main():
             t_f = timeit(lambda: F.attention(q.detach(), k.detach(), v.detach()))
             o = F.attention(q, k, v)
             g = rnd(B, T, Hq, D)
+            N.call("dla_attn_set_bwd_variant", 1)
+            t_b1 = timeit(lambda: torch.autograd.grad(o, qkv, g, retain_graph=True))
+            N.call("dla_attn_set_bwd_variant", 2)
+            t_b2 = timeit(lambda: torch.autograd.grad(o, qkv, g, retain_graph=True))
+            N.call("dla_attn_set_bwd_variant", 0)
             t_b = timeit(lambda: torch.autograd.grad(o, qkv, g, retain_graph=True))
-            qs, ks, vs = (t.detach().transpose(1, 2).contiguous() for t in (q, k, v))
-            t_sdpa = timeit(lambda: torch.nn.functional.scaled_dot_product_attention(qs, ks, vs, is_causal=True, enable_gqa=True))
-            rec = {"kernel": "attention", "B": B, "T": T, "Hq": Hq, "Hk": Hk, "D": D, "fwd_ms": t_f, "fwd_tflops": fl / t_f / 1e9, "fwd_gen1_ms": t_f1, "fwd_gen3_ms": t_f3,
-                   "bwd_ms": t_b, "bwd_tflops": 2.5 * fl / t_b / 1e9, "sdpa_fwd_ms": t_sdpa, "sdpa_fwd_tflops": fl / t_sdpa / 1e9}
+            # library arms on the same box: PyTorch SDPA (cuDNN / flash backends pick themselves) and flash-attn 2
+            qs, ks, vs = (t.detach().transpose(1, 2).contiguous().requires_grad_() for t in (q, k, v))
+            sdpa = lambda: torch.nn.functional.scaled_dot_product_attention(qs, ks, vs, is_causal=True, enable_gqa=True)
+            t_sdpa = timeit(lambda: sdpa())
+            os_ = sdpa()
+            gs = g.transpose(1, 2).contiguous()
+            t_sdpa_b = timeit(lambda: torch.autograd.grad(os_, (qs, ks, vs), gs, retain_graph=True))
+            t_fa = t_fa_b = None
+            try:
+                from flash_attn import flash_attn_func
+
+                qf, kf, vf = (t.detach().contiguous().requires_grad_() for t in (q, k, v))
+                t_fa = timeit(lambda: flash_attn_func(qf, kf, vf, causal=True))
+                of = flash_attn_func(qf, kf, vf, causal=True)
+                t_fa_b = timeit(lambda: torch.autograd.grad(of, (qf, kf, vf), g, retain_graph=True))
+            except Exception as e:  # not built for this arch / not importable
+                print(f"# flash_attn unavailable: {type(e).__name__}: {str(e)[:100]}", flush=True)
+            tf = lambda ms, mult=1.0: (mult * fl / ms / 1e9) if ms else None
+            rec = {"kernel": "attention", "B": B, "T": T, "Hq": Hq, "Hk": Hk, "D": D, "fwd_ms": t_f, "fwd_tflops": tf(t_f),
+                   "fwd_gen1_ms": t_f1, "fwd_gen3_ms": t_f3, "bwd_ms": t_b, "bwd_tflops": tf(t_b, 2.5), "bwd_gen1_ms": t_b1,
+                   "bwd_gen1_tflops": tf(t_b1, 2.5), "bwd_gen2_ms": t_b2, "bwd_gen2_tflops": tf(t_b2, 2.5), "sdpa_fwd_ms": t_sdpa, "sdpa_fwd_tflops": tf(t_sdpa), "sdpa_bwd_ms": t_sdpa_b,
+                   "sdpa_bwd_tflops": tf(t_sdpa_b, 2.5), "flash_attn2_fwd_ms": t_fa, "flash_attn2_fwd_tflops": tf(t_fa),
+                   "flash_attn2_bwd_ms": t_fa_b, "flash_attn2_bwd_tflops": tf(t_fa_b, 2.5),
+                   "note": "own bwd includes the delta / zeroing pre-pass and the fp32 -> bf16 dQ cast"}
             out.append(rec)
             print(json.dumps(rec), flush=True)
     if "elem" in which:
