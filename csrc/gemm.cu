@@ -285,10 +285,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tile_coords_ag(t, p.num_m_tiles, p.num_n_tiles, ag_first, m_blk, n_blk);
           // wait until the copy CTAs have landed this B tile in local memory, then order the generic-proxy
           // flag read before the async-proxy (TMA) reads of the tile
+          // Liveness: the copy CTAs are the lowest block ids of a grid of at most one CTA per SM, so they are resident
+          // whenever a compute CTA is (the hardware dispatches blocks in id order) — unless another kernel holds SMs
+          // for the whole time or a peer is dead.  The wait is therefore bounded by wall time (%globaltimer): after
+          // 30 s the kernel traps, which surfaces on the host as a launch failure instead of a GPU that never returns.
           uint32_t seen;
+          unsigned long long t0 = 0;
           do {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(p.ag_flags + n_blk) : "memory");
-            if (seen != p.ag_epoch) __nanosleep(100);
+            if (seen != p.ag_epoch) {
+              unsigned long long now;
+              asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+              if (t0 == 0) t0 = now;
+              if (now - t0 > 30000000000ULL) __trap();
+              __nanosleep(100);
+            }
           } while (seen != p.ag_epoch);
           asm volatile("fence.proxy.async;" ::: "memory");
         } else {

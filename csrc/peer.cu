@@ -99,6 +99,22 @@ __device__ __forceinline__ bool barrier_body(uint32_t* const* pads, int world, i
   return ok;
 }
 
+// One-sided halves of the flag exchange on an arbitrary row of `world` flag words (word offset flag_word in every pad):
+// mode 1 = publish `epoch` into slot `me` of every peer's row, mode 2 = wait until every rank's slot of MY row shows it.
+// Used around the gradient-bucket ring of streamed units: "I have finished reading your bucket" / "everybody has
+// finished reading mine, it may be refilled".
+__global__ void flag_row_kernel(uint32_t* const* pads, int world, int me, int flag_word, uint32_t epoch, int mode,
+                                unsigned long long timeout_ns) {
+  const int t = threadIdx.x;
+  if (t >= world) return;
+  if (mode == 1) {
+    __threadfence_system();
+    st_release_sys(pads[t] + flag_word + me, epoch);
+  } else if (!wait_flag(pads[me] + flag_word + t, epoch, timeout_ns)) {
+    note_timeout(nullptr);
+  }
+}
+
 __global__ void barrier_kernel(uint32_t* const* pads, int world, int me, int channel, uint32_t epoch,
                                unsigned long long timeout_ns, uint32_t* status) {
   const bool ok = barrier_body(pads, world, me, channel, epoch, timeout_ns);
@@ -375,6 +391,7 @@ struct UnitRsParams {
   float* sumsq_out;               // += sum(out^2) (nullable)
   uint32_t epoch;
   unsigned long long timeout_ns;
+  int accumulate;                 // grad_out += result (streamed units fold every micro-step into the fp32 shard)
 };
 
 template <bool kMC>
@@ -419,6 +436,11 @@ unit_rs_kernel(const UnitRsParams p) {
             ss += f[j] * f[j];
           }
           float* o = p.grad_out + i * 8;
+          if (p.accumulate) {
+            const float4 a0 = *reinterpret_cast<const float4*>(o), a1 = *reinterpret_cast<const float4*>(o + 4);
+            f[0] += a0.x; f[1] += a0.y; f[2] += a0.z; f[3] += a0.w;
+            f[4] += a1.x; f[5] += a1.y; f[6] += a1.z; f[7] += a1.w;
+          }
           *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
           *reinterpret_cast<float4*>(o + 4) = make_float4(f[4], f[5], f[6], f[7]);
         }
@@ -449,6 +471,11 @@ unit_rs_kernel(const UnitRsParams p) {
         ss += acc[j] * acc[j];
       }
       float* o = p.grad_out + i * 8;
+      if (p.accumulate) {
+        const float4 a0 = *reinterpret_cast<const float4*>(o), a1 = *reinterpret_cast<const float4*>(o + 4);
+        acc[0] += a0.x; acc[1] += a0.y; acc[2] += a0.z; acc[3] += a0.w;
+        acc[4] += a1.x; acc[5] += a1.y; acc[6] += a1.z; acc[7] += a1.w;
+      }
       *reinterpret_cast<float4*>(o) = make_float4(acc[0], acc[1], acc[2], acc[3]);
       *reinterpret_cast<float4*>(o + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
     }
@@ -787,9 +814,25 @@ int dla_peer_watch(void* host_mapped_word) {
   return 0;
 }
 
+int dla_peer_flag_row(uint32_t* const* pads, int world, int rank, int flag_word, uint32_t epoch, int mode, int timeout_ms,
+                      void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world && flag_word >= 0 && (mode == 1 || mode == 2),
+              DLA_E_BADARG, "peer_flag_row: bad arguments (world %d rank %d mode %d)", world, rank, mode);
+  flag_row_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(pads, world, rank, flag_word, epoch, mode, timeout_ns_of(timeout_ms));
+  return check_launch("peer_flag_row");
+}
+
 int dla_unit_reduce(uint32_t* const* pads, int flag_word, const void* mc_grads, const void* const* peer_grads, int world, int rank,
                     int64_t shard_elems, int64_t shard_offset, float scale, float* grad_out_fp32, float* sumsq_out, uint32_t epoch,
                     int timeout_ms, int max_blocks, void* stream) {
+  return dla_unit_reduce_acc(pads, flag_word, mc_grads, peer_grads, world, rank, shard_elems, shard_offset, scale, grad_out_fp32,
+                             sumsq_out, epoch, timeout_ms, max_blocks, 0, stream);
+}
+
+int dla_unit_reduce_acc(uint32_t* const* pads, int flag_word, const void* mc_grads, const void* const* peer_grads, int world,
+                        int rank, int64_t shard_elems, int64_t shard_offset, float scale, float* grad_out_fp32, float* sumsq_out,
+                        uint32_t epoch, int timeout_ms, int max_blocks, int accumulate, void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
   DLA_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, DLA_E_BADARG, "unit_reduce: bad world/rank %d/%d", world, rank);
   DLA_REQUIRE(shard_elems % 8 == 0 && shard_offset % 8 == 0 && flag_word >= 0, DLA_E_BADARG,
@@ -800,6 +843,7 @@ int dla_unit_reduce(uint32_t* const* pads, int flag_word, const void* mc_grads, 
   p.peer_grads = reinterpret_cast<const bf16* const*>(peer_grads);
   p.world = world; p.rank = rank; p.shard_elems = shard_elems; p.shard_offset = shard_offset; p.scale = scale;
   p.grad_out = grad_out_fp32; p.sumsq_out = sumsq_out; p.epoch = epoch; p.timeout_ns = timeout_ns_of(timeout_ms);
+  p.accumulate = accumulate;
   const int per_thread = mc_grads != nullptr ? 4 : 1;
   int64_t blocks = ((shard_elems >> 3) + 256 * per_thread - 1) / (256 * per_thread);
   if (max_blocks <= 0) max_blocks = kNumSMs * 2;

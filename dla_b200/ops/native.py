@@ -72,6 +72,8 @@ _SIGNATURES = {
     "dla_fused_gather_dpo": [P, P, I, I, P, P, P, P, I, F, F, c_uint32, P, P, P, P],
     "dla_adamw_mc": [P, P, P, P, P, I64, F, F, F, F, F, F, F, P, F, I, P],
     "dla_unit_reduce": [P, I, P, P, I, I, I64, I64, F, P, P, c_uint32, I, I, P],
+    "dla_unit_reduce_acc": [P, I, P, P, I, I, I64, I64, F, P, P, c_uint32, I, I, I, P],
+    "dla_peer_flag_row": [P, I, I, I, c_uint32, I, I, P],
     "dla_peer_norm_clip": [P, P, I, I, P, F, F, c_uint32, I, P, P, P],
     "dla_peer_push_mc": [P, P, I64, I64, P],
     "dla_peer_allreduce_mc": [P, I, I, I64, I64, F, P],

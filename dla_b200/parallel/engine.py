@@ -177,6 +177,21 @@ class Engine(ParamProvider):
             esz = _bytes(self.dtype)
             self._unit_ptrs = {u.name: torch.tensor([ptr + self.sbase[u.name] * esz for ptr in self.shard_arena.ptrs],
                                                     dtype=torch.int64, device=self.device) for u in self.units}
+            import os as _os2
+            self.stream_rs = self.trainable and _os2.environ.get("DLA_STREAM_RS", "1") != "0"
+            if self.stream_rs:
+                # gradient buckets of streamed units live in a small symmetric RING (peers sum them in place, in the
+                # switch): a bucket exists from the unit's backward until every peer has read its shard of it
+                self._ring_k = max(2, int(_os2.environ.get("DLA_STREAM_RING", "3")))
+                self._ring_p = max(self.P.values())
+                self.grad_ring = SymmetricArena(self.ctx, self._ring_k * self._ring_p, self.grad_dtype, zero=False)
+                self._ring_seq = 0
+                self._ring_prev: List[Optional[tuple]] = [None] * self._ring_k
+                self._ring_of: Dict[str, int] = {}
+                self._sflag_base = self.fc.claim_unit_rows(2 * len(self.units))     # rows: 2u = "bucket ready", 2u+1 = "shard read"
+                self._unit_index = {u.name: i for i, u in enumerate(self.units)}
+                self._srs_epoch = {u.name: 0 for u in self.units}
+                self._rs_stream = torch.cuda.Stream(device=self.device)
         for ui, u in enumerate(self.units):
             P, S = self.P[u.name], self.S[u.name]
             if self.fused:
@@ -337,7 +352,10 @@ class Engine(ParamProvider):
         if gb is None:
             if not (backward or torch.is_grad_enabled()):
                 return
-            gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
+            if self.fused_stream and getattr(self, "stream_rs", False) and backward:
+                gb = self._ring_bucket(unit)
+            else:
+                gb = torch.zeros(self.P[unit], dtype=self.grad_dtype, device=self.device)
             self.gradbuf[unit] = gb
         g = unit_views(gb, self._by_name[unit])
         if self.resident:
@@ -345,6 +363,42 @@ class Engine(ParamProvider):
         for k, t in w.items():
             t.requires_grad_(True)
             t._grad_slot = g[k]
+
+    def _ring_bucket(self, unit: str) -> torch.Tensor:
+        """Next slot of the symmetric gradient-bucket ring for ``unit`` (same sequence on every rank).  The slot's
+        previous occupant was reduced by kernels that read it from every peer: wait (on this stream) until all ranks
+        have published "shard read" for it, then clear the slot."""
+        slot = self._ring_seq % self._ring_k
+        self._ring_seq += 1
+        prev = self._ring_prev[slot]
+        if prev is not None:
+            self.fc.flag_wait(self._sflag_base + 16 * (2 * prev[0] + 1), prev[1])
+            self._ring_prev[slot] = None
+        gb = self.grad_ring.tensor[slot * self._ring_p: slot * self._ring_p + self.P[unit]]
+        gb.zero_()
+        self._ring_of[unit] = slot
+        return gb
+
+    def _launch_ring_reduce(self, unit: str) -> None:
+        """Streamed unit, fused path (a): the unit's bucket (a ring slot) is final on this rank.  On the side stream,
+        behind that point: one kernel announces it, waits for the peers' announcements, sums this rank's shard out of
+        all ranks' slots (in the switch when the ring has a multicast address) INTO the fp32 gradient shard, then a
+        second tiny kernel tells the peers that this rank is done reading their slots."""
+        slot = self._ring_of.pop(unit)
+        idx, S = self._unit_index[unit], self.S[unit]
+        self._srs_epoch[unit] += 1
+        ep = self._srs_epoch[unit]
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._rs_stream.wait_event(ev)
+        with torch.cuda.stream(self._rs_stream):
+            self.fc.reduce_unit(self.grad_ring, self._sflag_base + 16 * (2 * idx), ep, slot * self._ring_p + self.r * S, S, 1.0,
+                                self.gshard[unit], None, accumulate=True)
+            self.fc.flag_publish(self._sflag_base + 16 * (2 * idx + 1), ep)
+        self._ring_prev[slot] = (idx, ep)
+        self.stats["reduce_bytes"] += S * _bytes(self.grad_dtype) * (1 if self.grad_ring.mc_ptr else self.W - 1)
+        self.gradbuf[unit] = None
+        self._views.pop(unit, None)
 
     def _acquire_fused_stream(self, unit: str, backward: bool = False) -> Weights:
         """Streamed unit, fused path (b): big 2-D weights are NOT gathered here — each carries an ``_ag`` ticket
@@ -406,6 +460,8 @@ class Engine(ParamProvider):
             return self._launch_unit_reduce(unit)
         if self.fused or self.fused_ddp:
             return          # peers pull this bucket themselves inside the fused kernels
+        if self.fused_stream and unit in getattr(self, "_ring_of", {}):
+            return self._launch_ring_reduce(unit)
         gb = self.gradbuf[unit]
         nbytes = gb.numel() * gb.element_size()
         self.stats["reduce_bytes"] += nbytes
@@ -495,6 +551,8 @@ class Engine(ParamProvider):
         prescale = 1.0 / grad_divisor
         cuda = self.device.type == "cuda"
         self.sync_optimizer()
+        if self.fused_stream and getattr(self, "stream_rs", False):
+            torch.cuda.current_stream(self.device).wait_stream(self._rs_stream)     # the in-backward reduce-scatters
         self._materialize_fresh()
         overlap = cuda and self.overlap_optimizer and (self.W == 1 or self.fused)
         if overlap and self._opt_stream is None:
@@ -523,10 +581,14 @@ class Engine(ParamProvider):
                 g = self._local_grad(u.name)
                 N.call("dla_sumsq", N.ptr(g), g.numel(), int(g.dtype == torch.float32), N.ptr(self._sq_scratch),
                        N.ptr(self._sumsq), 1, s)
-            if self.W > 1:
-                dist.all_reduce(self._sumsq, group=self.ctx.group)
-            self._sumsq.mul_(prescale * prescale)
-            N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
+            if self.W > 1 and self.fused_stream:
+                # norm exchange + clip coefficient over peer memory: no NCCL launch in the optimizer phase
+                self.fc.norm_clip(self._sumsq, prescale, float(opt.max_grad_norm or 0.0), self._coef, self._norm)
+            else:
+                if self.W > 1:
+                    dist.all_reduce(self._sumsq, group=self.ctx.group)
+                self._sumsq.mul_(prescale * prescale)
+                N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
             self._last_grad_norm = self._norm
         else:
             sq = torch.zeros((), dtype=torch.float64)

@@ -160,11 +160,21 @@ class FusedComm:
 
     # ---------------------------------------------------------------- (a) v2: in-backward, per unit
     def reduce_unit(self, grads: SymmetricArena, flag_word: int, epoch: int, offset: int, n: int, scale: float,
-                    out_fp32: torch.Tensor, sumsq: Optional[torch.Tensor], timeout_ms: int = 30000, max_blocks: int = 0) -> None:
+                    out_fp32: torch.Tensor, sumsq: Optional[torch.Tensor], timeout_ms: int = 30000, max_blocks: int = 0,
+                    accumulate: bool = False) -> None:
         """Reduce-scatter of one unit on the CURRENT stream: waits (inside the kernel) until every rank has flagged
-        this unit's bucket complete for ``epoch``, then sums this rank's shard — in NVSwitch when possible."""
-        N.call("dla_unit_reduce", self.pads.ptrs_dev, flag_word, grads.mc_ptr or None, grads.ptrs_dev, self.W, self.r, n, offset,
-               scale, N.ptr(out_fp32), N.ptr(sumsq), epoch, timeout_ms, max_blocks, N.stream_ptr(self.ctx.device))
+        this unit's bucket complete for ``epoch``, then sums this rank's shard — in NVSwitch when possible.
+        ``accumulate``: add to ``out_fp32`` instead of overwriting it."""
+        N.call("dla_unit_reduce_acc", self.pads.ptrs_dev, flag_word, grads.mc_ptr or None, grads.ptrs_dev, self.W, self.r, n, offset,
+               scale, N.ptr(out_fp32), N.ptr(sumsq), epoch, timeout_ms, max_blocks, int(accumulate), N.stream_ptr(self.ctx.device))
+
+    def flag_publish(self, flag_word: int, epoch: int) -> None:
+        """Tell every peer (on the current stream, after everything enqueued so far) that this rank reached ``epoch``."""
+        N.call("dla_peer_flag_row", self.pads.ptrs_dev, self.W, self.r, flag_word, epoch, 1, 0, N.stream_ptr(self.ctx.device))
+
+    def flag_wait(self, flag_word: int, epoch: int, timeout_ms: int = 30000) -> None:
+        """Hold the current stream until every rank has published ``epoch`` on this row."""
+        N.call("dla_peer_flag_row", self.pads.ptrs_dev, self.W, self.r, flag_word, epoch, 2, timeout_ms, N.stream_ptr(self.ctx.device))
 
     def norm_clip(self, sumsq_local: torch.Tensor, prescale: float, max_norm: float, coef: torch.Tensor, norm: torch.Tensor) -> None:
         """Global grad norm + clip coefficient from every rank's partial ``sum(g^2)`` (reset to 0 afterwards)."""

@@ -333,6 +333,17 @@ int dla_unit_reduce(uint32_t* const* pads, int flag_word, const void* mc_grads, 
                     int world, int rank, int64_t shard_elems, int64_t shard_offset, float scale,
                     float* grad_out_fp32, float* sumsq_out, uint32_t epoch, int timeout_ms, int max_blocks,
                     void* stream);
+/* dla_unit_reduce with accumulate != 0: grad_out_fp32 += scale * sum (streamed ZeRO-3 units fold every micro-step's
+ * reduce-scatter into the fp32 gradient shard).  R: R/config/deepspeed_zero3.json:5-15 (stage 3, overlap_comm). */
+int dla_unit_reduce_acc(uint32_t* const* pads, int flag_word, const void* mc_grads, const void* const* peer_grads,
+                        int world, int rank, int64_t shard_elems, int64_t shard_offset, float scale,
+                        float* grad_out_fp32, float* sumsq_out, uint32_t epoch, int timeout_ms, int max_blocks,
+                        int accumulate, void* stream);
+/* One half of a flag exchange on a row of `world` flag words at word offset flag_word of every pad: mode 1 publishes
+ * `epoch` to every peer, mode 2 waits until all ranks have published it to this rank.  Brackets the reuse of a
+ * gradient-bucket ring slot that peers read directly. */
+int dla_peer_flag_row(uint32_t* const* pads, int world, int rank, int flag_word, uint32_t epoch, int mode,
+                      int timeout_ms, void* stream);
 /* Global grad-norm + clip coefficient without an NCCL launch: exchanges every rank's partial sum(g^2) over peer memory
  * (bufs: per-rank fp32 [2][world]), sums in rank order, writes norm = sqrt(total) * prescale and
  * coef = min(1, max_norm / (norm + 1e-6)) (0 when non-finite), and resets *sumsq_local to 0.

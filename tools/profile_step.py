@@ -44,10 +44,11 @@ with torch.profiler.profile(activities=[torch.profiler.ProfilerActivity.CUDA]) a
     step()
     torch.cuda.synchronize()
 agg = defaultdict(lambda: [0.0, 0])
+fills = []
 for ev in prof.events():
     if ev.device_type == torch.autograd.DeviceType.CUDA:
         name = ev.name
-        for key in ("gemm2_kernel", "gemm_kernel", "attn_fwd", "attn_bwd_kernel", "attn_bwd_prep", "attn_bwd_dq", "rmsnorm_fwd", "rmsnorm_bwd",
+        for key in ("gemm2_kernel", "gemm_kernel", "attn_fwd", "attn_bwd2_kernel", "attn_bwd_kernel", "attn_bwd_prep", "attn_bwd_dq", "rmsnorm_fwd", "rmsnorm_bwd",
                     "colsum", "rope", "swiglu_fwd", "swiglu_bwd", "adamw", "sumsq", "embedding", "logprob_grad", "logprob_combine",
                     "Memset", "Memcpy"):
             if key in name:
@@ -61,12 +62,17 @@ for ev in prof.events():
             import re
             mm = re.search(r"(\w+Functor|\w+_kernel_cuda|FillFunctor|direct_copy_kernel|CatArray\w*|reduce_kernel|index\w*)", name)
             name = "torch:" + (mm.group(1) if mm else name[:60])
-        agg[name][0] += ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
+        dur = ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
+        if name in ("torch:FillFunctor", "Memset", "Memcpy"):
+            fills.append((dur, name))
+        agg[name][0] += dur
         agg[name][1] += 1
 rows = sorted(((k, v[0] / 1e3, v[1]) for k, v in agg.items()), key=lambda r: -r[1])
 total = sum(r[1] for r in rows)
 print(f"total kernel time {total:.1f} ms")
 for k, ms, n in rows[:30]:
     print(f"{ms:9.2f} ms {100 * ms / total:5.1f}%  x{n:5d}  {k[:100]}")
+fills.sort(reverse=True)
+print("largest fill / memset / memcpy events (us):", [(round(d, 1), n) for d, n in fills[:12]], "count", len(fills))
 Path(ROOT / "gpurun_out").mkdir(exist_ok=True)
 json.dump({"total_ms": total, "rows": rows[:40]}, open(ROOT / "gpurun_out" / "step_breakdown.json", "w"), indent=1)
