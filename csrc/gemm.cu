@@ -618,6 +618,8 @@ static int build_maps(CUtensorMap* tmA, CUtensorMap* tmB, const void* A, const v
 namespace dla {
 int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
                    int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream);
+int gemm2_swiglu_dispatch(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda, int64_t ldb,
+                          int64_t ldgu, int64_t ldact, cudaStream_t stream);
 void gemm2_set_tail_split(int on);
 }
 
@@ -689,6 +691,16 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   if (!a_mn_major && b_mn_major) return launch<false, true, kStore>(tmA, tmB, tmC, p, s);
   if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, tmC, p, s);
   return launch<true, true, kStore>(tmA, tmB, tmC, p, s);
+}
+
+int dla_gemm_swiglu_bf16(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda, int64_t ldb,
+                         int64_t ldgu, int64_t ldact, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M > 0 && F > 0 && K > 0 && K % 8 == 0, DLA_E_BADARG, "gemm_swiglu: bad shape M=%d F=%d K=%d", M, F, K);
+  DLA_REQUIRE(F % 128 == 0 && M >= 256, DLA_E_UNSUPP, "gemm_swiglu: needs F %% 128 == 0 and M >= 256 (F=%d, M=%d)", F, M);
+  DLA_REQUIRE(((uintptr_t)ACT & 15) == 0 && (ldact * 2) % 16 == 0 && (GU == nullptr || ((((uintptr_t)GU & 15) == 0) && (ldgu * 2) % 16 == 0)),
+              DLA_E_BADARG, "gemm_swiglu: outputs must be 16-byte aligned with 16-byte row pitch");
+  return gemm2_swiglu_dispatch(A, B, GU, ACT, M, F, K, lda, ldb, ldgu, ldact, (cudaStream_t)stream);
 }
 
 int dla_ag_gemm_bf16(const void* A, const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t b_offset,

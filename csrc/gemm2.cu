@@ -8,6 +8,12 @@
 //   warp 1  MMA issuer (leader only); tcgen05.commit multicasts "slot free" / "accumulator ready" to both CTAs
 //   warps 2-5 epilogue (each CTA drains its own TMEM half through staged smem + TMA store / reduce-add)
 //
+// kSwiGLU (gate/up projection of a Llama MLP, B = [2F, K] with the gate rows first): the cluster tile is made of the
+// SAME 128 feature columns of gate (CTA 0's half of B) and up (CTA 1's half), so each CTA ends up with gate in TMEM
+// columns [0,128) and up in [128,256) for its 128 rows and the epilogue emits act = silu(gate) * up directly — the
+// separate SwiGLU pass (read 2F, write F per token) disappears; gate/up themselves are stored only when a backward
+// will need them.  Replaces K5 of SURVEY §2.6.2 as a stand-alone kernel on the forward path.
+//
 // Same operand-layout support as gemm.cu (K-major / MN-major A and B).  Selected by dla_gemm_bf16 when the
 // problem has at least one full wave of 256x256 tiles (see gemm.cu) or forced with dla_gemm_set_variant(2).
 #include <math.h>
@@ -40,6 +46,8 @@ struct Params {
   // items over disjoint K slices, one per cluster, combined by TMA reduce-add (those tiles are zero-filled by
   // zero_tail_kernel first unless the caller accumulates).  tail_splits <= 1: off.
   int tail_tiles, tail_splits;
+  int F;            // kSwiGLU: features per half (N = 2F); num_n_tiles counts 128-wide feature blocks
+  int store_gu;     // kSwiGLU: also store gate / up (bf16) through tmC for the backward
 };
 
 // work item w -> (tile, K-block range).  Items below `full` are whole tiles; the rest are K slices of the tail tiles,
@@ -98,10 +106,10 @@ __device__ __forceinline__ void tma_load_2d_to(void* smem_dst, const CUtensorMap
       : "memory");
 }
 
-template <bool kAMN, bool kBMN>
+template <bool kAMN, bool kBMN, bool kSwiGLU = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-             const __grid_constant__ CUtensorMap tmC, const Params p) {
+             const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmD, const Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* epi_smem = smem + kStages * STAGE_BYTES;
@@ -149,7 +157,9 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         const Work wk = work_item(w, p, num_tiles, num_kb);
         int m_blk, n_blk;
         tile_coords(wk.tile, p.num_m_tiles, p.num_n_tiles, m_blk, n_blk);
-        const int m0 = m_blk * 256 + (int)cta * BM, n0 = n_blk * BN + (int)cta * BNH;
+        const int m0 = m_blk * 256 + (int)cta * BM;
+        // kSwiGLU: CTA 0 stages the gate rows of feature block n_blk, CTA 1 the up rows of the same block
+        const int n0 = kSwiGLU ? (int)cta * p.F + n_blk * BNH : n_blk * BN + (int)cta * BNH;
         for (int kb = wk.kb0; kb < wk.kb1; ++kb) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * STAGE_BYTES;
@@ -225,6 +235,52 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
       const int gc = p.c_fp32 ? 32 : 64;
       const int n_groups = BN / gc;
       uint8_t* stage_base = epi_smem + (warp - 2) * 2 * 4096;
+      if constexpr (kSwiGLU) {
+        // act[:, n_blk*128 + 64 gi .. +64) = silu(gate) * up from TMEM columns [64 gi, +64) and [128 + 64 gi, +64)
+        int nbuf = 0;
+        auto emit = [&](const CUtensorMap* tm, const uint32_t* r, int c0) {      // 64 fp32 values of this lane's row -> bf16 tile store
+          uint8_t* buf = stage_base + (nbuf & 1) * 4096;
+          ++nbuf;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          uint8_t* myrow = buf + lane * 128;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 v;
+            v.x = pack2(r[8 * c], r[8 * c + 1]);
+            v.y = pack2(r[8 * c + 2], r[8 * c + 3]);
+            v.z = pack2(r[8 * c + 4], r[8 * c + 5]);
+            v.w = pack2(r[8 * c + 6], r[8 * c + 7]);
+            *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = v;
+          }
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            if (r0 < p.M) tc::tma_store_2d(tm, buf, c0, r0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        };
+#pragma unroll 1
+        for (int gi = 0; gi < 2; ++gi) {
+          uint32_t g[64], u[64];
+          tc::tmem_ld_32x32(taddr + gi * 64, g);
+          tc::tmem_ld_32x32(taddr + gi * 64 + 32, g + 32);
+          tc::tmem_ld_32x32(taddr + 128 + gi * 64, u);
+          tc::tmem_ld_32x32(taddr + 128 + gi * 64 + 32, u + 32);
+          tc::tmem_ld_wait();
+          const int fc0 = n_blk * BNH + gi * 64;
+          if (p.store_gu) {
+            emit(&tmC, g, fc0);
+            emit(&tmC, u, p.F + fc0);
+          }
+#pragma unroll
+          for (int c = 0; c < 64; ++c) {
+            const float gv = __uint_as_float(g[c]);
+            g[c] = __float_as_uint(gv / (1.f + __expf(-gv)) * __uint_as_float(u[c]));
+          }
+          emit(&tmD, g, fc0);
+        }
+      } else
 #pragma unroll 1
       for (int gi = 0; gi < n_groups; ++gi) {
         uint8_t* buf = stage_base + (gi & 1) * 4096;
@@ -302,9 +358,10 @@ zero_tail_kernel(uint8_t* __restrict__ C, int64_t ld_bytes, int esz, int M, int 
     }
 }
 
-template <bool kAMN, bool kBMN>
-static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
-  auto kern = gemm2_kernel<kAMN, kBMN>;
+template <bool kAMN, bool kBMN, bool kSwiGLU = false>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmD, const Params& p,
+                  cudaStream_t stream) {
+  auto kern = gemm2_kernel<kAMN, kBMN, kSwiGLU>;
   static bool attr_set = false;
   if (!attr_set) {
     DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
@@ -312,8 +369,8 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
   }
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
   const int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
-  kern<<<2 * clusters, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, p);
-  return check_launch("gemm2_bf16");
+  kern<<<2 * clusters, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmD, p);
+  return check_launch(kSwiGLU ? "gemm2_swiglu" : "gemm2_bf16");
 }
 
 }  // namespace gemm2
@@ -360,10 +417,33 @@ int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, i
       }
     }
   }
-  if (!a_mn && !b_mn) return launch<false, false>(tmA, tmB, tmC, p, stream);
-  if (!a_mn && b_mn) return launch<false, true>(tmA, tmB, tmC, p, stream);
-  if (a_mn && !b_mn) return launch<true, false>(tmA, tmB, tmC, p, stream);
-  return launch<true, true>(tmA, tmB, tmC, p, stream);
+  if (!a_mn && !b_mn) return launch<false, false>(tmA, tmB, tmC, tmC, p, stream);
+  if (!a_mn && b_mn) return launch<false, true>(tmA, tmB, tmC, tmC, p, stream);
+  if (a_mn && !b_mn) return launch<true, false>(tmA, tmB, tmC, tmC, p, stream);
+  return launch<true, true>(tmA, tmB, tmC, tmC, p, stream);
+}
+
+// act[M, F] = silu(A W_gate^T) * (A W_up^T) with W = [gate rows | up rows] = B[2F, K]; gu (nullable) receives gate | up
+int gemm2_swiglu_dispatch(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda, int64_t ldb,
+                          int64_t ldgu, int64_t ldact, cudaStream_t stream) {
+  using namespace gemm2;
+  CUtensorMap tmA, tmB, tmC, tmD;
+  int rc;
+  if ((rc = make_tmap_2d_bf16(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmB, B, (uint64_t)K, (uint64_t)(2 * F), (uint64_t)ldb, BK, BNH))) return rc;
+  if ((rc = make_tmap_2d(&tmD, ACT, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (uint64_t)F, (uint64_t)M, (uint64_t)ldact, 64, 32))) return rc;
+  if (GU != nullptr) {
+    if ((rc = make_tmap_2d(&tmC, GU, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (uint64_t)(2 * F), (uint64_t)M, (uint64_t)ldgu, 64, 32))) return rc;
+  } else {
+    tmC = tmD;
+  }
+  Params p{};
+  p.M = M; p.N = 2 * F; p.K = K; p.c_fp32 = 0; p.accumulate = 0;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = F / BNH;
+  p.F = F;
+  p.store_gu = GU != nullptr;
+  return launch<false, false, true>(tmA, tmB, tmC, tmD, p, stream);
 }
 
 }  // namespace dla

@@ -384,6 +384,68 @@ class _SwiGLU(Function):
         return dgu.view(ctx.shape)
 
 
+class _LinearSwiGLU(Function):
+    """``silu(x W_gate^T) * (x W_up^T)`` with the activation computed in the epilogue of the gate/up GEMM (2-CTA tcgen05
+    kernel, ``csrc/gemm2.cu``): no separate SwiGLU pass over the ``[M, 2F]`` projection.  gate | up are stored only when
+    a backward follows; the backward is the usual SwiGLU backward + dgrad + wgrad (into the weight's gradient slot)."""
+
+    @staticmethod
+    def forward(ctx, x, w):
+        x2 = _c(x.reshape(-1, x.shape[-1]))
+        M, K = x2.shape
+        F2 = w.shape[0]
+        need_bwd = ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+        act = torch.empty(M, F2 // 2, dtype=BF16, device=x.device)
+        gu = torch.empty(M, F2, dtype=BF16, device=x.device) if need_bwd else None
+        N.call("dla_gemm_swiglu_bf16", N.ptr(x2), N.ptr(w), N.ptr(gu), N.ptr(act), M, F2 // 2, K, x2.stride(0), w.stride(0),
+               F2, F2 // 2, _s(x))
+        if need_bwd:
+            ctx.save_for_backward(x2, w, gu)
+        ctx.wref = w
+        ctx.xshape = x.shape
+        return act.view(*x.shape[:-1], F2 // 2)
+
+    @staticmethod
+    def backward(ctx, dact):
+        x2, w, gu = ctx.saved_tensors
+        d2 = _c(dact.reshape(gu.shape[0], -1))
+        dgu = torch.empty_like(gu)
+        N.call("dla_swiglu_bwd", N.ptr(d2), N.ptr(gu), N.ptr(dgu), gu.shape[0], gu.shape[1] // 2, _s(gu))
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dgu, w, b_mn=True).view(ctx.xshape)
+        if ctx.needs_input_grad[1]:
+            slot, acc = _slot_gemm(ctx.wref)
+            if slot is not None:
+                gemm(dgu, x2, a_mn=True, b_mn=True, out=slot, accumulate=acc)
+            else:
+                dw = gemm(dgu, x2, a_mn=True, b_mn=True)
+        return dx, dw
+
+
+FUSE_SWIGLU = [True]        # A/B switch (tests, DLA_FUSE_SWIGLU=0)
+
+
+def linear_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
+    """``swiglu(linear(x, w_gu))`` for ``w_gu = [gate rows | up rows]``; on CUDA, when the shape suits the 2-CTA kernel
+    (F % 128 == 0, at least half a wave of 256 x 128-feature tiles), the activation is fused into the GEMM epilogue."""
+    F2, K = w_gu.shape
+    M = x.numel() // x.shape[-1]
+    ag = getattr(w_gu, "_ag", None)
+    fused = (x.is_cuda and FUSE_SWIGLU[0] and x.dtype == BF16 and w_gu.dtype == BF16 and F2 % 256 == 0 and M >= 256 and K % 8 == 0
+             and ((M + 255) // 256) * (F2 // 256) >= 74 and w_gu.stride(1) == 1 and w_gu.stride(0) % 8 == 0
+             and w_gu.data_ptr() % 16 == 0 and (ag is None or ag.done))
+    if not fused:
+        return swiglu(linear(x, w_gu))
+    return _LinearSwiGLU.apply(x, w_gu)
+
+
+import os as _os
+
+if _os.environ.get("DLA_FUSE_SWIGLU", "1") == "0":
+    FUSE_SWIGLU[0] = False
+
+
 def swiglu(gu: torch.Tensor) -> torch.Tensor:
     if not gu.is_cuda:
         return R.swiglu(gu)

@@ -137,6 +137,12 @@ int dla_seq_mean_bwd(const float* dseq, const int64_t* mask, float* dtok, int B,
 int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                   int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
                   int c_fp32, int accumulate, void* stream);
+/* Gate/up projection of a gated MLP with the activation in the GEMM epilogue (2-CTA kernel): B = [2F, K] holds the gate
+ * rows then the up rows; ACT[M, F] = silu(A B_gate^T) * (A B_up^T), computed from the fp32 accumulators.  GU (nullable,
+ * [M, 2F] bf16) additionally receives gate | up for a backward pass.  Needs F % 128 == 0, M >= 256 (DLA_E_UNSUPP
+ * otherwise: run dla_gemm_bf16 + dla_swiglu_fwd).  R: the HF Llama MLP under R/src/training/train_dpo.py:32 (K1 + K5). */
+int dla_gemm_swiglu_bf16(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda,
+                         int64_t ldb, int64_t ldgu, int64_t ldact, void* stream);
 /* 0 = auto, 1 = 1-CTA 128x256, 2 = 2-CTA pair 256x256 (debug / benchmarking switch). */
 int dla_gemm_set_variant(int variant);
 

@@ -641,3 +641,43 @@ def test_distill_kl_rows(native_lib, K, V, temp):
     (ref * coef).sum().backward()
     err = (dl.float() - s.grad).norm() / s.grad.norm()
     assert err < 1e-2, f"distill grad relative error {err:.3g}"
+
+
+@pytest.mark.parametrize("M,F_,K", [(2048, 1280, 512), (2304, 2048, 1024), (8192, 14336, 4096)])
+def test_gate_up_gemm_with_swiglu_epilogue(native_lib, M, F_, K):
+    """csrc/gemm2.cu kSwiGLU: act = silu(x Wg^T) * (x Wu^T) out of the GEMM epilogue against the fp32 composition, forward
+    (with and without the stored gate/up) and backward (dx, dW through the saved gate/up)."""
+    from dla_b200.ops import native as N
+
+    torch.manual_seed(31)
+    x = _rand(M, K, scale=0.5)
+    w = _rand(2 * F_, K, scale=K ** -0.5)
+    before = N.launch_count()
+    with torch.no_grad():
+        act0 = F.linear_swiglu(x, w)                       # no backward: gate/up are not stored at all
+    assert N.launch_count() - before == 1, "the fused path is one kernel"
+    gu_ref = x.float() @ w.float().t()
+    act_ref = torch.nn.functional.silu(gu_ref[:, :F_]) * gu_ref[:, F_:]
+    _rel(act0, act_ref, 6e-3, what="fused swiglu act (no grad)")
+    xa, wa = x.clone().requires_grad_(), w.clone().requires_grad_()
+    act = F.linear_swiglu(xa, wa)
+    assert torch.equal(act, act0)
+    g = _rand(M, F_, scale=0.1)
+    act.backward(g)
+    if M * F_ * K > 2e11:
+        return            # the fp32 autograd reference of the big shape would need > 10 GB; forward was checked above
+    xr, wr = x.float().requires_grad_(), w.float().requires_grad_()
+    gr = xr @ wr.t()
+    (torch.nn.functional.silu(gr[:, :F_]) * gr[:, F_:] * g.float()).sum().backward()
+    _rel(xa.grad, xr.grad, 1.5e-2, what="fused swiglu dx")
+    _rel(wa.grad, wr.grad, 1.5e-2, what="fused swiglu dW")
+    # and it agrees with the unfused pair of kernels
+    F.FUSE_SWIGLU[0] = False
+    try:
+        xb, wb = x.clone().requires_grad_(), w.clone().requires_grad_()
+        act_b = F.linear_swiglu(xb, wb)
+        act_b.backward(g)
+    finally:
+        F.FUSE_SWIGLU[0] = True
+    _rel(act, act_b, 6e-3, what="fused vs unfused act")
+    _rel(xa.grad, xb.grad, 1e-2, what="fused vs unfused dx")

@@ -35,6 +35,8 @@ ap.add_argument("--warmup", type=int, default=2)
 ap.add_argument("--seq", type=int, default=4096)
 ap.add_argument("--mb", type=int, default=2)
 ap.add_argument("--new-tokens", type=int, default=64)
+ap.add_argument("--algo", default="reinforce", choices=["reinforce", "ppo"],
+                help="ppo config: the reference's sequence-level REINFORCE update, or clipped PPO with value head + GAE")
 args = ap.parse_args()
 ctx = init_distributed()
 dev, W = ctx.device, ctx.world_size
@@ -191,7 +193,14 @@ elif args.what == "ppo":
     from dla_b200.optim import AdamWConfig
     from dla_b200.rollout import Generator
 
-    pol = load_causal_lm(args.model, ctx, plan, name="policy")
+    from dla_b200.models.config import resolve_model_config
+
+    extra = None
+    if args.algo == "ppo":
+        from dla_b200.models.reward import value_head_unit
+
+        extra = [value_head_unit(resolve_model_config(args.model))]
+    pol = load_causal_lm(args.model, ctx, plan, name="policy", extra_units=extra)
     ref = load_causal_lm(args.model, ctx, plan, trainable=False, gradient_checkpointing=False, name="reference")
     rm, _ = build_reward_model(args.model, ctx, plan, trainable=False, gradient_checkpointing=False, name="reward")
     rm.eval()
@@ -201,6 +210,43 @@ elif args.what == "ppo":
     gen = Generator(pol.model)
     opt = AdamWConfig(lr=1e-6, betas=(0.9, 0.95))
     t = {}
+    eng = pol.engine
+    fc = getattr(eng, "fc", None) if (getattr(eng, "fused", False) or getattr(eng, "fused_ddp", False)) else None
+
+    class _Loop:            # what cli.train_rlhf._ppo_update needs from TrainLoop
+        global_step = 0
+
+        def micro_step(self, fn):
+            loss = fn()
+            loss.backward()
+            eng.finish_backward()
+            eng.optimizer_step(opt, grad_divisor=float(W))
+            self.global_step += 1
+            return loss.detach()
+
+    loop = _Loop()
+    if args.algo == "ppo":
+        from dla_b200.cli.train_rlhf import _ppo_update
+        from dla_b200.models.reward import ValueHead
+
+        vhead = ValueHead(eng)
+        pc = {"epochs": 1, "mini_batch_size": 4, "target_kl": 0.1, "gamma": 1.0, "lam": 0.95, "cliprange": 0.2,
+              "cliprange_value": 0.2, "vf_coef": 0.5}       # R/config/rlhf_config.yaml:12-22 (mini_batch 32 / 8 ranks)
+
+    def step_ppo():
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        out = gen.generate(ids, torch.ones_like(ids), max_new_tokens=Tn, do_sample=True, temperature=0.7, top_p=0.9, seed=1,
+                           eos_token_id=-1, pad_token_id=0)
+        torch.cuda.synchronize()
+        t["rollout"] = time.perf_counter() - t0
+        with torch.no_grad():
+            scores = rm(out.sequences, out.attention_mask).float()
+            ref_tok = ref.model.token_logprobs(out.sequences, out.attention_mask)
+        info = {}
+        _ppo_update(loop, pol, vhead, out.sequences, out.attention_mask, out.response_mask, ref_tok, scores, pc, 0.1, info, ctx, fc)
+        torch.cuda.synchronize()
+        t["total"] = time.perf_counter() - t0
 
     def step():
         torch.cuda.synchronize()
@@ -213,13 +259,20 @@ elif args.what == "ppo":
             scores = rm(out.sequences, out.attention_mask).float()
             ref_lp = sequence_logprobs(ref.model, out.sequences, out.attention_mask)
         p_lp = sequence_logprobs(pol.model, out.sequences, out.attention_mask)
-        loss, kl, rw = reinforce_step(p_lp, ref_lp, scores, 0.1)
+        if fc is not None:      # fused path (c): cross-rank gather + global baseline + loss in one peer-memory kernel
+            from dla_b200.parallel.fused import fused_reinforce_loss
+
+            loss, _ = fused_reinforce_loss(fc, p_lp, ref_lp, scores, 0.1)
+        else:
+            loss, kl, rw = reinforce_step(p_lp, ref_lp, scores, 0.1)
         loss.backward()
         pol.engine.finish_backward()
         pol.engine.optimizer_step(opt, grad_divisor=float(W))
         torch.cuda.synchronize()
         t["total"] = time.perf_counter() - t0
 
+    if args.algo == "ppo":
+        step = step_ppo
     for _ in range(args.warmup):
         step()
     rs, ts = [], []
@@ -228,7 +281,8 @@ elif args.what == "ppo":
         rs.append(t["rollout"])
         ts.append(t["total"])
     r, tot = ctx.max_over_ranks(sum(rs) / len(rs)), ctx.max_over_ranks(sum(ts) / len(ts))
-    emit({"config": "ppo_reinforce", "prompts_per_rank": B, "prompt_len": Tp, "new_tokens": Tn, "rollout_s": r,
+    emit({"config": "ppo_clipped_value_gae" if args.algo == "ppo" else "ppo_reinforce", "prompts_per_rank": B,
+          "fused_gather": fc is not None, "updates_per_step": (B // 4) if args.algo == "ppo" else 1, "prompt_len": Tp, "new_tokens": Tn, "rollout_s": r,
           "rollout_tokens_per_s": B * Tn * W / r, "decode_ms_per_token": r / Tn * 1e3, "score_and_update_s": tot - r, "step_s": tot,
           "peak_hbm_gb": torch.cuda.max_memory_allocated(dev) / (1 << 30)})
 ctx.barrier()
