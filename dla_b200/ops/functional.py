@@ -86,11 +86,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
           and out.stride(1) == 1 and out.dtype in (BF16, torch.float32)
           and (not a_mn or M % 8 == 0) and (not b_mn or Nn % 8 == 0))
     if not ok:
-        if a.is_cuda and a.dtype == BF16:
-            _note_fallback("gemm", (M, Nn, K))
+        if a.is_cuda and a.dtype == BF16 and b.dtype == BF16 and out.dtype in (BF16, torch.float32):
+            return _gemm_padded(a, b, a_mn, b_mn, out, accumulate, M, Nn, K)
         am = a.t() if a_mn else a
         bm = b if b_mn else b.t()
-        res = torch.matmul(am.to(torch.float32) if not a.is_cuda else am, bm.to(torch.float32) if not a.is_cuda else bm)
+        res = torch.matmul(am.to(torch.float32), bm.to(torch.float32))      # CPU tensors / non-bf16 dtypes only
         if accumulate:
             out.add_(res.to(out.dtype))
         else:
@@ -103,6 +103,37 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         return out
     N.call("dla_gemm_bf16", N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, a.stride(0), b.stride(0), out.stride(0),
            int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), _s(a))
+    return out
+
+
+def _gemm_padded(a, b, a_mn, b_mn, out, accumulate, M, Nn, K):
+    """Shapes the TMA descriptors cannot address directly (K, an MN-major extent or a row pitch that is not a multiple
+    of 8 elements, a base that is not 16-byte aligned): the operands are copied into zero-padded staging buffers with
+    conforming extents and the SAME tcgen05 kernel runs on them; zero padding along K adds nothing, padded rows /
+    columns of the result are dropped.  (Round 1 sent these shapes to a library matmul.)"""
+    up8 = lambda n: (n + 7) // 8 * 8
+    Kp = up8(K)
+    Mp = up8(M) if a_mn else M
+    Np = up8(Nn) if b_mn else Nn
+
+    def stage(t, mn, rows_mn, rows_mn_p):
+        want = (Kp, rows_mn_p) if mn else (t.shape[0], Kp)
+        if tuple(t.shape) == want and t.stride(1) == 1 and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0:
+            return t
+        buf = torch.zeros(want, dtype=BF16, device=t.device)
+        buf[: t.shape[0], : t.shape[1]].copy_(t)
+        return buf
+
+    a2, b2 = stage(a, a_mn, M, Mp), stage(b, b_mn, Nn, Np)
+    direct = (Mp == M and Np == Nn and out.stride(1) == 1)
+    tgt = out if direct else torch.empty(Mp, Np, dtype=out.dtype, device=out.device)
+    N.call("dla_gemm_bf16", N.ptr(a2), N.ptr(b2), N.ptr(tgt), Mp, Np, Kp, a2.stride(0), b2.stride(0), tgt.stride(0),
+           int(a_mn), int(b_mn), int(tgt.dtype == torch.float32), int(accumulate and direct), _s(a2))
+    if not direct:
+        if accumulate:
+            out.add_(tgt[:M, :Nn])
+        else:
+            out.copy_(tgt[:M, :Nn])
     return out
 
 
@@ -137,18 +168,6 @@ def linear_residual(x: torch.Tensor, w: torch.Tensor, resid: torch.Tensor, bias:
                M, w.shape[0], K, x2.stride(0), w.stride(0), out.stride(0), r2.stride(0), 0, int(_STATIC_WEIGHTS[0]), _s(x2))
         return out.view(resid.shape)
     return resid + linear(x, w, bias)
-
-
-_FALLBACKS: dict = {}
-
-
-def _note_fallback(op: str, shape) -> None:
-    key = (op, tuple(shape))
-    if key not in _FALLBACKS:
-        _FALLBACKS[key] = 0
-        import warnings
-        warnings.warn(f"{op}{tuple(shape)} is not TMA-addressable; using the library GEMM for this shape")
-    _FALLBACKS[key] += 1
 
 
 class _Linear(Function):
