@@ -72,6 +72,26 @@ total = sum(r[1] for r in rows)
 print(f"total kernel time {total:.1f} ms")
 for k, ms, n in rows[:30]:
     print(f"{ms:9.2f} ms {100 * ms / total:5.1f}%  x{n:5d}  {k[:100]}")
+# GPU idle time: gaps between consecutive kernels on the device timeline (all streams merged), attributed to the kernel
+# that FOLLOWS the gap (the one the host was late to launch)
+evs = sorted(((ev.time_range.start, ev.time_range.end, ev.name) for ev in prof.events()
+              if ev.device_type == torch.autograd.DeviceType.CUDA), key=lambda e: e[0])
+idle = defaultdict(lambda: [0.0, 0])
+busy_until, t_first = None, None
+for st_, en_, nm in evs:
+    if busy_until is None:
+        busy_until, t_first = en_, st_
+        continue
+    gap = st_ - busy_until
+    if gap > 2.0:
+        short = nm.split("(")[0][-48:]
+        idle[short][0] += gap
+        idle[short][1] += 1
+    busy_until = max(busy_until, en_)
+tot_idle = sum(v[0] for v in idle.values())
+print(f"device timeline {(busy_until - t_first) / 1e3:.1f} ms, idle {tot_idle / 1e3:.1f} ms in gaps > 2 us; top followers of a gap:")
+for k, v in sorted(idle.items(), key=lambda kv: -kv[1][0])[:14]:
+    print(f"   {v[0] / 1e3:7.2f} ms  x{v[1]:4d}  avg {v[0] / v[1]:6.1f} us  before {k}")
 fills.sort(reverse=True)
 print("largest fill / memset / memcpy events (us):", [(round(d, 1), n) for d, n in fills[:12]], "count", len(fills))
 Path(ROOT / "gpurun_out").mkdir(exist_ok=True)
