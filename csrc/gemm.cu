@@ -589,10 +589,15 @@ static int g_auto_2cta = 1;      // measured on B200 (profiles/kernels_r1_2cta.j
 template <bool kAMN, bool kBMN, int kEpi>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const Params& p, cudaStream_t stream) {
   auto kern = gemm_kernel<kAMN, kBMN, kEpi>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute: set it once on every device
+  // this process launches on (the allocation-free entry point promises to work on each device it is called on)
+  static std::atomic<unsigned long long> attr_devices{0};
+  int dev = 0;
+  DLA_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ULL << (dev & 63);
+  if (!(attr_devices.load(std::memory_order_relaxed) & bit)) {
     DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set = true;
+    attr_devices.fetch_or(bit, std::memory_order_relaxed);
   }
   const int num_tiles = p.num_m_tiles * p.num_n_tiles * (p.k_splits > 1 ? p.k_splits : 1);
   int grid = num_tiles < kNumSMs ? num_tiles : kNumSMs;
