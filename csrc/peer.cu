@@ -29,6 +29,25 @@ __device__ uint32_t g_peer_timeout_flag = 0;
 // optional mirror in pinned host memory (dla_peer_watch): the training loop polls it without touching the device
 __device__ uint32_t* g_peer_status_host = nullptr;
 
+// Debug build (DLA_BUILD_DEFINES="-DDLA_PEER_DEBUG" python -m dla_b200.ops.build --force): sequence-number assertions on
+// the signal pad.  Epochs on a flag row advance by exactly one per use and no rank can be more than one use ahead of a
+// peer (every use ends in a wait for all ranks), so a flag that jumps, repeats or runs ahead by two means a protocol bug
+// (a missed launch on some rank, two owners of one row, a row reused before its readers left) — trap instead of
+// computing on torn data.  SURVEY §5.2: the stand-in for a race detector on the one protocol compute-sanitizer
+// cannot see (it is cross-GPU).
+#ifdef DLA_PEER_DEBUG
+#define DLA_PEER_ASSERT(cond, what, a, b)                                                             \
+  do {                                                                                                \
+    if (!(cond)) {                                                                                    \
+      printf("dla peer protocol violation: %s (%u vs %u) block %d thread %d\n", what, (unsigned)(a), \
+             (unsigned)(b), (int)blockIdx.x, (int)threadIdx.x);                                       \
+      __trap();                                                                                       \
+    }                                                                                                 \
+  } while (0)
+#else
+#define DLA_PEER_ASSERT(cond, what, a, b) ((void)0)
+#endif
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -78,10 +97,12 @@ __device__ __forceinline__ void multimem_st16(void* mc, const uint4& v) {
 // stretch when the SM clock drops under a power cap.
 __device__ __forceinline__ bool wait_flag(const uint32_t* flag, uint32_t epoch, unsigned long long timeout_ns) {
   const unsigned long long t0 = globaltimer_ns();
-  while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+  uint32_t seen;
+  while ((int32_t)((seen = ld_acquire_sys(flag)) - epoch) < 0) {
     if (timeout_ns > 0 && globaltimer_ns() - t0 > timeout_ns) return false;
     __nanosleep(64);
   }
+  DLA_PEER_ASSERT((int32_t)(seen - epoch) <= 1, "a peer is two or more uses ahead on this flag", seen, epoch);
   return true;
 }
 
@@ -92,6 +113,9 @@ __device__ __forceinline__ bool barrier_body(uint32_t* const* pads, int world, i
   const int t = threadIdx.x;
   bool ok = true;
   if (t < world) {
+    // my own slot of my own pad holds what I published last time: the sequence must advance by exactly one
+    DLA_PEER_ASSERT(t != me || ld_acquire_sys(pads[me] + channel * world + me) + 1u == epoch,
+                    "barrier epoch does not follow the previous one", ld_acquire_sys(pads[me] + channel * world + me), epoch);
     __threadfence_system();
     st_release_sys(pads[t] + channel * world + me, epoch);
     ok = wait_flag(pads[me] + channel * world + t, epoch, timeout_ns);
@@ -401,6 +425,8 @@ unit_rs_kernel(const UnitRsParams p) {
   __shared__ int s_ok;
   const int t = threadIdx.x;
   if (blockIdx.x == 0 && t < p.world) {
+    DLA_PEER_ASSERT(t != p.rank || ld_acquire_sys(p.pads[p.rank] + p.flag_word + p.rank) + 1u == p.epoch,
+                    "unit flag epoch does not follow the previous one", ld_acquire_sys(p.pads[p.rank] + p.flag_word + p.rank), p.epoch);
     __threadfence_system();
     st_release_sys(p.pads[t] + p.flag_word + p.rank, p.epoch);
   }

@@ -26,6 +26,10 @@ NVCC_FLAGS = [
 ]
 
 
+# extra -D switches for diagnostic builds, e.g. DLA_BUILD_DEFINES="-DDLA_PEER_DEBUG" (signal-pad sequence assertions)
+NVCC_FLAGS += [f for f in os.environ.get("DLA_BUILD_DEFINES", "").split() if f.startswith("-D")]
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and Path(cand).exists():
