@@ -675,6 +675,9 @@ class Engine(ParamProvider):
                         N.call("dla_adamw", *args, N.ptr(sh) + esz * lo, *tail)
                         fc.push_shard(sh[lo:hi], self.param_arena, off + lo)
                     self.stats["allgather_bytes"] += (hi - lo) * esz * (1 if mc else self.W - 1)
+        elif self._train_ranges is not None:
+            raise NotImplementedError("freeze_except is implemented on the in-backward reduce-scatter path (the default); "
+                                      "unset DLA_RS_IN_BACKWARD=0 / DLA_OVERLAP_OPT=0 to use it with the fused engine")
         elif clip_on or self._moment_flag:        # the single-kernel reduce+AdamW keeps fp32 moments only
             self._sumsq.zero_()
             for u in self.units:

@@ -476,3 +476,34 @@ def test_in_backward_reduce_scatter_engine_matches_nccl(tmp_path, world):
         assert ln == pytest.approx(lf, abs=3e-3), (tag, ln, lf)
         assert gn == pytest.approx(gf, rel=3e-2), tag
         assert float((pn - pf).norm() / pn.norm()) < 3e-3, tag
+
+
+def _watchdog_worker(rank, world, port):
+    ctx = _init(rank, world, port)
+    from dla_b200.parallel.fused import FusedComm
+
+    fc = FusedComm.get(ctx)
+    fc.barrier(0)
+    torch.cuda.synchronize()
+    fc.check()                                   # healthy so far
+    if rank == 0:
+        # rank 1 never enters this barrier (a wedged peer): the wait gives up after 300 ms of wall time, the kernel
+        # mirrors the fact into pinned host memory, and check() turns it into an exception without a device query
+        import time
+
+        t0 = time.perf_counter()
+        fc.barrier(7, timeout_ms=300)
+        torch.cuda.synchronize()
+        waited = time.perf_counter() - t0
+        assert 0.25 < waited < 5.0, waited
+        with pytest.raises(RuntimeError, match="timed out"):
+            fc.check()
+        with pytest.raises(RuntimeError, match="timed out"):
+            fc.check(sync=True)
+    ctx.barrier()                                # NCCL: both ranks leave together
+
+
+def test_watchdog_turns_a_missing_peer_into_an_exception():
+    """a peer that stops taking part must not hang the others forever or let them compute on half-exchanged
+    data — the flag wait is bounded by wall time and the training loop's per-step poll raises."""
+    mp.spawn(_watchdog_worker, args=(2, _free_port()), nprocs=2, join=True)
