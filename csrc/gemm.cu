@@ -509,6 +509,24 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             if (j < nvalid) cs += exp2f((__uint_as_float(r[j]) - nm) * kLog2e);
           sum = sum * exp2f((mx - nm) * kLog2e) + cs;
           mx = nm;
+          if (p.C != nullptr && row < p.M) {
+            // keep the logits (bf16) for the backward: it then skips the recomputation GEMM.  64 contiguous bytes per
+            // lane and chunk; a tile's stores are spread over its 24 us of MMA time, so the LSU cost is noise.
+            bf16* dst = reinterpret_cast<bf16*>(p.C) + (int64_t)row * p.ldc + col0;
+            if (nvalid == 32) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                float f[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) f[q] = __uint_as_float(r[j + q]);
+                st8(dst + j, pack8(f));
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j < nvalid) dst[j] = __float2bfloat16(__uint_as_float(r[j]));
+            }
+          }
           if ((rel >> 5) == ch && rel >= 0) {
 #pragma unroll
             for (int j = 0; j < 32; ++j)
@@ -746,7 +764,15 @@ size_t dla_lmhead_scratch_bytes(int M, int V) {
 
 int dla_lmhead_logprob(const void* X, const void* W, const int64_t* labels, int M, int V, int K, int64_t ldx,
                        int64_t ldw, void* scratch, float* logp, float* lse, void* stream) {
+  return dla_lmhead_logprob_keep(X, W, labels, M, V, K, ldx, ldw, scratch, logp, lse, nullptr, 0, stream);
+}
+
+int dla_lmhead_logprob_keep(const void* X, const void* W, const int64_t* labels, int M, int V, int K, int64_t ldx,
+                            int64_t ldw, void* scratch, float* logp, float* lse, void* logits_out, int64_t ld_logits,
+                            void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(logits_out == nullptr || (ld_logits % 8 == 0 && ld_logits >= V && ((uintptr_t)logits_out & 15) == 0), DLA_E_BADARG,
+              "lmhead_logprob: kept logits need a 16-byte aligned buffer with a row pitch that is a multiple of 8 and >= V");
   DLA_REQUIRE(M > 0 && V > 0 && K > 0 && K % 8 == 0, DLA_E_BADARG, "lmhead_logprob: bad shape M=%d V=%d K=%d", M, V, K);
   DLA_REQUIRE(scratch != nullptr && logp != nullptr, DLA_E_BADARG, "lmhead_logprob: scratch and logp are required");
   CUtensorMap tmA, tmB;
@@ -759,6 +785,8 @@ int dla_lmhead_logprob(const void* X, const void* W, const int64_t* labels, int 
   p.labels = labels;
   p.partials = reinterpret_cast<float2*>(scratch);
   p.picked = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + (size_t)p.num_n_tiles * M * sizeof(float2));
+  p.C = logits_out;
+  p.ldc = ld_logits;
   cudaStream_t s = (cudaStream_t)stream;
   rc = launch<false, false, kLogprob>(tmA, tmB, CUtensorMap{}, p, s);
   if (rc) return rc;

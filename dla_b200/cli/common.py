@@ -108,11 +108,35 @@ class TrainLoop:
                 self.engine.optimizer_step(self.opt, lr=lr, grad_divisor=float(self.ctx.world_size * self.accum)
                                            if self.engine.sharding != "none" else 1.0)
             self.optimizer_steps += 1
+            if self.optimizer_steps == 1:
+                self._size_kept_activations()
         self.global_step += 1
         self.micro_steps += 1
         if self.tokens_fn is not None and batch is not None:
             self._tok_since += int(self.tokens_fn(batch))
         return loss.detach()
+
+    def _size_kept_activations(self) -> None:
+        """``hardware.keep_activations``: once the first update has shown the allocator's steady state, spend the free
+        HBM on keeping activations (and the lm_head logits) instead of recomputing them in backward.  Sized for the
+        LONGEST batch the config allows (micro_batch x max_seq_length, x2 for preference pairs), so shorter batches only
+        leave more slack; ``off`` keeps the reference's recompute-everything behaviour."""
+        mode = self.plan.keep_activations
+        eng = self.engine
+        if mode in ("off", False, None, 0, "0") or self.ctx.device.type != "cuda" or not hasattr(eng, "auto_no_recompute"):
+            return
+        mc, oc = self.cfg.get("model", {}) or {}, self.cfg.get("optimization", {}) or self.cfg.get("ppo", {}) or {}
+        max_len = int(mc.get("max_seq_length") or (self.cfg.get("data", {}) or {}).get("max_seq_length") or 0)
+        mb = int(oc.get("micro_batch_size") or oc.get("mini_batch_size") or oc.get("batch_size") or 0)
+        if not max_len or not mb:
+            return
+        tokens = mb * max_len * (2 if self.phase in ("dpo", "reward") else 1)
+        if isinstance(mode, int) or (isinstance(mode, str) and mode.isdigit()):
+            k = eng.set_no_recompute_layers(int(mode))
+        else:
+            k = eng.auto_no_recompute(tokens, reserve_gb=self.plan.keep_reserve_gb)
+        self.ctx.print0(f"[{self.phase}] keeping the activations of the last {k} layer(s) instead of recomputing them "
+                        f"(hardware.keep_activations={mode})")
 
     def after_step(self, loss: torch.Tensor, extra: Optional[Dict[str, Any]] = None, sampler: Any = None) -> None:
         """Logging / checkpoint cadence of the reference loops."""

@@ -133,6 +133,11 @@ class HardwarePlan:
     min_num_params: int = 0
     num_processes: Optional[int] = None
     optimizer_state_dtype: str = "fp32"
+    # spend free HBM on NOT recomputing: "auto" (after the first update, keep the activations of as many trailing layers —
+    # and the lm_head logits — as fit with `keep_reserve_gb` to spare), "off" (recompute everything, the reference's
+    # behaviour), or an integer number of layers
+    keep_activations: Any = "auto"
+    keep_reserve_gb: float = 16.0
     raw: Dict[str, Any] = field(default_factory=dict)
 
 
@@ -145,6 +150,8 @@ def resolve_hardware(cfg: Dict[str, Any], config_dir: Optional[Path] = None) -> 
     plan.resident_params = hw.get("resident_params")
     plan.num_processes = hw.get("num_processes")
     plan.optimizer_state_dtype = hw.get("optimizer_state_dtype", "fp32")
+    plan.keep_activations = hw.get("keep_activations", "auto")
+    plan.keep_reserve_gb = float(hw.get("keep_reserve_gb", 16.0))
     sharding = hw.get("sharding")
     ds = hw.get("deepspeed_config")
     if ds:

@@ -5,6 +5,8 @@ There is no third path: a CUDA tensor without the native library raises.
 """
 from __future__ import annotations
 
+import os as _os
+
 import math
 from typing import Optional, Tuple
 
@@ -459,8 +461,6 @@ def linear_swiglu(x: torch.Tensor, w_gu: torch.Tensor) -> torch.Tensor:
     return _LinearSwiGLU.apply(x, w_gu)
 
 
-import os as _os
-
 if _os.environ.get("DLA_FUSE_SWIGLU", "1") == "0":
     FUSE_SWIGLU[0] = False
 
@@ -726,15 +726,33 @@ class _LinearLogprob(Function):
         scratch = N.workspace("lmhead", nbytes, h.device)
         logp = torch.empty(M, dtype=torch.float32, device=h.device)
         lse = torch.empty(M, dtype=torch.float32, device=h.device)
-        N.call("dla_lmhead_logprob", N.ptr(h), N.ptr(w), N.ptr(labels), M, V, K, h.stride(0), w.stride(0),
-               N.ptr(scratch), N.ptr(logp), N.ptr(lse), _s(h))
-        ctx.save_for_backward(h, w, labels, lse)
+        Vp = (V + 7) // 8 * 8
+        # memory-for-compute: with HBM to spare (KEEP_LOGITS, set by Engine.auto_no_recompute or DLA_KEEP_LOGITS=1) the
+        # epilogue also stores the bf16 logits and the backward skips its recomputation GEMM
+        kept = None
+        if KEEP_LOGITS[0] and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]):   # (grad mode is off inside forward)
+            kept = torch.empty(M, Vp, dtype=BF16, device=h.device)
+        N.call("dla_lmhead_logprob_keep", N.ptr(h), N.ptr(w), N.ptr(labels), M, V, K, h.stride(0), w.stride(0),
+               N.ptr(scratch), N.ptr(logp), N.ptr(lse), N.ptr(kept), Vp, _s(h))
+        if kept is not None:
+            ctx.save_for_backward(h, w, labels, lse, kept)
+        else:
+            ctx.save_for_backward(h, w, labels, lse)
+        ctx.kept = kept is not None
+        ctx.kept_state = [False]        # set once the backward has turned the kept logits into gradients in place
         ctx.wref = w
         return logp, lse
 
     @staticmethod
     def backward(ctx, g, _g_lse):
-        h, w, labels, lse = ctx.saved_tensors
+        saved = ctx.saved_tensors
+        h, w, labels, lse = saved[:4]
+        kept = saved[4] if ctx.kept else None
+        if kept is not None:
+            if ctx.kept_state[0]:
+                raise RuntimeError("linear_logprob: the kept logits were turned into gradients by the first backward; "
+                                   "run with DLA_KEEP_LOGITS=0 (F.KEEP_LOGITS[0] = False) to backpropagate twice")
+            ctx.kept_state[0] = True
         M, K = h.shape
         V = w.shape[0]
         g = _c(g.float())
@@ -747,13 +765,19 @@ class _LinearLogprob(Function):
         wtgt = slot if slot is not None else dw
         Vp = (V + 7) // 8 * 8
         chunk = min(LOGPROB_BWD_CHUNK, M)
-        buf = N.workspace("lmhead_bwd", chunk * Vp * 2, h.device).view(BF16)[: chunk * Vp].view(chunk, Vp)
+        if kept is None:
+            buf = N.workspace("lmhead_bwd", chunk * Vp * 2, h.device).view(BF16)[: chunk * Vp].view(chunk, Vp)
         for s in range(0, M, chunk):
             e = min(s + chunk, M)
             n = e - s
-            dl = buf[:n].narrow(1, 0, V)            # [n, V] view, row pitch Vp
-            gemm(h[s:e], w, out=dl)                  # recompute bf16 logits for this row chunk
-            N.call("dla_logprob_grad_inplace", N.ptr(buf), N.ptr(lse[s:e]), N.ptr(labels[s:e]), N.ptr(g[s:e]),
+            if kept is None:
+                rows = buf[:n]
+                dl = rows.narrow(1, 0, V)           # [n, V] view, row pitch Vp
+                gemm(h[s:e], w, out=dl)              # recompute bf16 logits for this row chunk
+            else:
+                rows = kept[s:e]                     # the forward kept them: transformed in place, chunk by chunk
+                dl = rows.narrow(1, 0, V)
+            N.call("dla_logprob_grad_inplace", N.ptr(rows), N.ptr(lse[s:e]), N.ptr(labels[s:e]), N.ptr(g[s:e]),
                    n, V, Vp, _s(h))
             if dh is not None:
                 gemm(dl, w, b_mn=True, out=dh[s:e])
@@ -761,6 +785,9 @@ class _LinearLogprob(Function):
                 gemm(dl, h[s:e], a_mn=True, b_mn=True, out=wtgt, accumulate=acc)
                 acc = True               # later row chunks add to the first one
         return dh, dw, None
+
+
+KEEP_LOGITS = [_os.environ.get("DLA_KEEP_LOGITS", "0") == "1"]
 
 
 def linear_logprob(h: torch.Tensor, w: torch.Tensor, labels: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:

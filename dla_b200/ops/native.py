@@ -46,6 +46,7 @@ _SIGNATURES = {
     "dla_gemm_swiglu_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],
     "dla_set_device": [I],
     "dla_lmhead_logprob": [P, P, P, I, I, I, I64, I64, P, P, P, P],
+    "dla_lmhead_logprob_keep": [P, P, P, I, I, I, I64, I64, P, P, P, P, I64, P],
     "dla_logprob_grad_inplace": [P, P, P, P, I, I, I64, P],
     "dla_attn_fwd": [P, P, P, P, P, I, I, I, I, I] + [I64] * 9 + [P, F, I, P],
     "dla_attn_bwd": [P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I] + [I64] * 9 + [P, F, I, P],

@@ -267,7 +267,22 @@ class Engine(ParamProvider):
         torch.cuda.synchronize(self.device)
         free, _ = torch.cuda.mem_get_info(self.device)
         free += torch.cuda.memory_reserved(self.device) - torch.cuda.memory_allocated(self.device)
-        k = int(max(0, free - reserve_gb * (1 << 30)) // max(per_layer, 1))
+        budget = max(0, free - reserve_gb * (1 << 30))
+        k = int(budget // max(per_layer, 1))
+        # the lm_head's bf16 logits (2 bytes x tokens x vocab) are kept only from what is left once EVERY layer keeps its
+        # activations: measured at N=1 (Llama-3-8B), giving up a layer (2.6 GB, 2.7 ms of recomputation) for the logits
+        # (2.1 GB, one GEMM of the backward) was a net loss of 3 ms; with sharded state (N >= 2) there is room for both
+        from dla_b200.ops import functional as _F
+
+        n_layers = sum(1 for u in self.units if u.name.startswith("layer."))
+        logits_bytes = tokens * (-(-cfg.vocab_size // 8) * 8) * 2
+        keep_logits = self.trainable and k >= n_layers and budget - n_layers * per_layer >= logits_bytes
+        if self.ctx.world_size > 1:
+            t = torch.tensor([int(keep_logits)], device=self.device)
+            dist.all_reduce(t, dist.ReduceOp.MIN, group=self.ctx.group)
+            keep_logits = bool(t.item())
+        if "DLA_KEEP_LOGITS" not in __import__("os").environ:
+            _F.KEEP_LOGITS[0] = keep_logits
         if self.ctx.world_size > 1:     # every rank must take the same decision
             t = torch.tensor([k], device=self.device)
             dist.all_reduce(t, dist.ReduceOp.MIN, group=self.ctx.group)

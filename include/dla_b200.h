@@ -154,6 +154,11 @@ int dla_gemm_set_variant(int variant);
 int dla_lmhead_logprob(const void* X, const void* W, const int64_t* labels, int M, int V, int K,
                        int64_t ldx, int64_t ldw, void* scratch, float* logp, float* lse,
                        void* stream);
+/* Same, additionally storing the bf16 logits (row pitch ld_logits >= V, multiple of 8) when logits_out != NULL: a
+ * memory-for-compute trade for the backward, which then skips its recomputation GEMM (2 bytes x M x V). */
+int dla_lmhead_logprob_keep(const void* X, const void* W, const int64_t* labels, int M, int V, int K,
+                            int64_t ldx, int64_t ldw, void* scratch, float* logp, float* lse,
+                            void* logits_out, int64_t ld_logits, void* stream);
 size_t dla_lmhead_scratch_bytes(int M, int V);
 /* In place on a bf16 logits chunk [Mc, V]: logits <- grow[m] * (onehot(label) - softmax(logits)),
  * using the saved lse (backward of the op above, chunked). */

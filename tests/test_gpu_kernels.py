@@ -681,3 +681,32 @@ def test_gate_up_gemm_with_swiglu_epilogue(native_lib, M, F_, K):
         F.FUSE_SWIGLU[0] = True
     _rel(act, act_b, 6e-3, what="fused vs unfused act")
     _rel(xa.grad, xb.grad, 1e-2, what="fused vs unfused dx")
+
+
+def test_lm_head_logprob_with_kept_logits(native_lib):
+    """``F.KEEP_LOGITS``: the fused log-prob epilogue also stores the bf16 logits and the backward skips its recomputation
+    GEMM — same values and gradients as the recomputing path; a second backward through the consumed logits is refused."""
+    torch.manual_seed(51)
+    M, V, K = 520, 50257, 256
+    h, w = _rand(M, K), _rand(V, K, scale=K ** -0.5)
+    labels = torch.randint(0, V, (M,), device=DEV)
+    labels[::9] = -100
+    wgt = torch.randn(M, device=DEV)
+    res = {}
+    for keep in (False, True):
+        F.KEEP_LOGITS[0] = keep
+        try:
+            ha, wa = h.clone().requires_grad_(), w.clone().requires_grad_()
+            logp, lse = F.linear_logprob(ha, wa, labels)
+            (logp * wgt).sum().backward(retain_graph=keep)
+            if keep:
+                with pytest.raises(RuntimeError, match="kept logits"):
+                    (logp * wgt).sum().backward()
+        finally:
+            F.KEEP_LOGITS[0] = False
+        res[keep] = (logp.detach(), lse.detach(), ha.grad, wa.grad)
+    assert torch.equal(res[True][0], res[False][0]) and torch.equal(res[True][1], res[False][1])
+    # the kept logits are the forward kernel's fp32 sums rounded to bf16, the recomputed ones come from a second GEMM whose
+    # summation order differs: a few logits round the other way (1 bf16 ulp), nothing more
+    _rel(res[True][2], res[False][2], 8e-3, what="dh kept vs recomputed")
+    _rel(res[True][3], res[False][3], 8e-3, what="dW kept vs recomputed")
