@@ -643,6 +643,8 @@ int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, i
                    int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream);
 int gemm2_swiglu_dispatch(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda, int64_t ldb,
                           int64_t ldgu, int64_t ldact, cudaStream_t stream);
+int gemm2_swiglu_bwd_dispatch(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H, int64_t lddy,
+                              int64_t ldw, int64_t ldgu, int64_t lddgu, cudaStream_t stream);
 void gemm2_set_tail_split(int on);
 }
 
@@ -724,6 +726,16 @@ int dla_gemm_swiglu_bf16(const void* A, const void* B, void* GU, void* ACT, int 
   DLA_REQUIRE(((uintptr_t)ACT & 15) == 0 && (ldact * 2) % 16 == 0 && (GU == nullptr || ((((uintptr_t)GU & 15) == 0) && (ldgu * 2) % 16 == 0)),
               DLA_E_BADARG, "gemm_swiglu: outputs must be 16-byte aligned with 16-byte row pitch");
   return gemm2_swiglu_dispatch(A, B, GU, ACT, M, F, K, lda, ldb, ldgu, ldact, (cudaStream_t)stream);
+}
+
+int dla_gemm_swiglu_bwd_bf16(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H, int64_t lddy,
+                             int64_t ldw, int64_t ldgu, int64_t lddgu, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M >= 256 && F > 0 && H > 0 && H % 8 == 0 && F % 64 == 0, DLA_E_UNSUPP,
+              "gemm_swiglu_bwd: needs M >= 256, H %% 8 == 0, F %% 64 == 0 (M=%d F=%d H=%d)", M, F, H);
+  DLA_REQUIRE((((uintptr_t)GU | (uintptr_t)dGU) & 15) == 0 && ldgu % 8 == 0 && lddgu % 8 == 0, DLA_E_BADARG,
+              "gemm_swiglu_bwd: gate|up buffers must be 16-byte aligned with row pitches that are multiples of 8");
+  return gemm2_swiglu_bwd_dispatch(dY, Wdown, GU, dGU, M, F, H, lddy, ldw, ldgu, lddgu, (cudaStream_t)stream);
 }
 
 int dla_ag_gemm_bf16(const void* A, const void* const* peer_shards, void* unit_full, int64_t shard_elems, int64_t b_offset,

@@ -14,6 +14,10 @@
 // separate SwiGLU pass (read 2F, write F per token) disappears; gate/up themselves are stored only when a backward
 // will need them.  Replaces K5 of SURVEY §2.6.2 as a stand-alone kernel on the forward path.
 //
+// kFuse == 2 (dgrad of the down projection): the epilogue turns its d(act) tile into d(gate) and d(up) on the spot — it
+// reads the saved gate / up values of the same rows and columns and stores both halves of d[gate | up]; d(act) itself
+// never reaches memory and the separate SwiGLU-backward pass disappears.
+//
 // Same operand-layout support as gemm.cu (K-major / MN-major A and B).  Selected by dla_gemm_bf16 when the
 // problem has at least one full wave of 256x256 tiles (see gemm.cu) or forced with dla_gemm_set_variant(2).
 #include <math.h>
@@ -46,8 +50,10 @@ struct Params {
   // items over disjoint K slices, one per cluster, combined by TMA reduce-add (those tiles are zero-filled by
   // zero_tail_kernel first unless the caller accumulates).  tail_splits <= 1: off.
   int tail_tiles, tail_splits;
-  int F;            // kSwiGLU: features per half (N = 2F); num_n_tiles counts 128-wide feature blocks
-  int store_gu;     // kSwiGLU: also store gate / up (bf16) through tmC for the backward
+  int F;            // kFuse 1: features per half (N = 2F), num_n_tiles counts 128-wide feature blocks; kFuse 2: N = F
+  int store_gu;     // kFuse 1: also store gate / up (bf16) through tmC for the backward
+  const bf16* gu;   // kFuse 2: saved [M, 2F] gate | up
+  int64_t ldgu;
 };
 
 // work item w -> (tile, K-block range).  Items below `full` are whole tiles; the rest are K slices of the tail tiles,
@@ -106,10 +112,11 @@ __device__ __forceinline__ void tma_load_2d_to(void* smem_dst, const CUtensorMap
       : "memory");
 }
 
-template <bool kAMN, bool kBMN, bool kSwiGLU = false>
+template <bool kAMN, bool kBMN, int kFuse = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
              const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmD, const Params p) {
+  constexpr bool kSwiGLU = kFuse == 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* epi_smem = smem + kStages * STAGE_BYTES;
@@ -280,6 +287,66 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           }
           emit(&tmD, g, fc0);
         }
+      } else if constexpr (kFuse == 2) {
+        // d(gate), d(up) from this CTA's d(act) tile [128 rows x 256 feature columns] and the saved gate / up
+        const int row = r0 + lane;
+        int nbuf = 0;
+        auto emit = [&](const uint32_t* r, int c0) {
+          uint8_t* buf = stage_base + (nbuf & 1) * 4096;
+          ++nbuf;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+          uint8_t* myrow = buf + lane * 128;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            uint4 v;
+            v.x = pack2(r[8 * c], r[8 * c + 1]);
+            v.y = pack2(r[8 * c + 2], r[8 * c + 3]);
+            v.z = pack2(r[8 * c + 4], r[8 * c + 5]);
+            v.w = pack2(r[8 * c + 6], r[8 * c + 7]);
+            *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = v;
+          }
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            if (r0 < p.M) tc::tma_store_2d(&tmD, buf, c0, r0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        };
+#pragma unroll 1
+        for (int gi = 0; gi < 4; ++gi) {
+          const int c0 = col_base + gi * 64;
+          if (c0 >= p.F) break;                     // (F % 64 == 0: a group is all in or all out)
+          // request the saved gate / up values of this lane's row first: they arrive while the TMEM load is in flight
+          uint4 gq[8], uq[8];
+          const bool rv = row < p.M;
+          const bf16* gp = p.gu + (int64_t)(rv ? row : 0) * p.ldgu + c0;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            gq[c] = *reinterpret_cast<const uint4*>(gp + c * 8);
+            uq[c] = *reinterpret_cast<const uint4*>(gp + p.F + c * 8);
+          }
+          uint32_t d[64], o[64];
+          tc::tmem_ld_32x32(taddr + gi * 64, d);
+          tc::tmem_ld_32x32(taddr + gi * 64 + 32, d + 32);
+          tc::tmem_ld_wait();
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            float g8[8], u8[8];
+            unpack8(*reinterpret_cast<const bf16x8*>(&gq[c]), g8);
+            unpack8(*reinterpret_cast<const bf16x8*>(&uq[c]), u8);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float da = __uint_as_float(d[c * 8 + e]);
+              const float sg = 1.f / (1.f + __expf(-g8[e]));
+              const float silu = g8[e] * sg;
+              o[c * 8 + e] = __float_as_uint(da * silu);                                       // d(up)
+              d[c * 8 + e] = __float_as_uint(da * u8[e] * sg * (1.f + g8[e] * (1.f - sg)));   // d(gate)
+            }
+          }
+          emit(d, c0);
+          emit(o, p.F + c0);
+        }
       } else
 #pragma unroll 1
       for (int gi = 0; gi < n_groups; ++gi) {
@@ -358,10 +425,10 @@ zero_tail_kernel(uint8_t* __restrict__ C, int64_t ld_bytes, int esz, int M, int 
     }
 }
 
-template <bool kAMN, bool kBMN, bool kSwiGLU = false>
+template <bool kAMN, bool kBMN, int kFuse = 0>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmD, const Params& p,
                   cudaStream_t stream) {
-  auto kern = gemm2_kernel<kAMN, kBMN, kSwiGLU>;
+  auto kern = gemm2_kernel<kAMN, kBMN, kFuse>;
   static bool attr_set = false;
   if (!attr_set) {
     DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
@@ -370,7 +437,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
   const int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
   kern<<<2 * clusters, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmD, p);
-  return check_launch(kSwiGLU ? "gemm2_swiglu" : "gemm2_bf16");
+  return check_launch(kFuse == 1 ? "gemm2_swiglu" : kFuse == 2 ? "gemm2_swiglu_bwd" : "gemm2_bf16");
 }
 
 }  // namespace gemm2
@@ -443,7 +510,27 @@ int gemm2_swiglu_dispatch(const void* A, const void* B, void* GU, void* ACT, int
   p.num_n_tiles = F / BNH;
   p.F = F;
   p.store_gu = GU != nullptr;
-  return launch<false, false, true>(tmA, tmB, tmC, tmD, p, stream);
+  return launch<false, false, 1>(tmA, tmB, tmC, tmD, p, stream);
+}
+
+// d[gate | up][M, 2F] = swiglu_bwd(dY[M, H] @ Wdown[H, F], GU[M, 2F]) — the dgrad of the down projection with the SwiGLU
+// backward as its epilogue
+int gemm2_swiglu_bwd_dispatch(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H, int64_t lddy,
+                              int64_t ldw, int64_t ldgu, int64_t lddgu, cudaStream_t stream) {
+  using namespace gemm2;
+  CUtensorMap tmA, tmB, tmD;
+  int rc;
+  if ((rc = make_tmap_2d_bf16(&tmA, dY, (uint64_t)H, (uint64_t)M, (uint64_t)lddy, BK, BM))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmB, Wdown, (uint64_t)F, (uint64_t)H, (uint64_t)ldw, 64, BK))) return rc;      // MN-major B
+  if ((rc = make_tmap_2d(&tmD, dGU, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (uint64_t)(2 * F), (uint64_t)M, (uint64_t)lddgu, 64, 32))) return rc;
+  Params p{};
+  p.M = M; p.N = F; p.K = H; p.c_fp32 = 0; p.accumulate = 0;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = (F + BN - 1) / BN;
+  p.F = F;
+  p.gu = reinterpret_cast<const bf16*>(GU);
+  p.ldgu = ldgu;
+  return launch<false, true, 2>(tmA, tmB, tmD, tmD, p, stream);
 }
 
 }  // namespace dla

@@ -353,7 +353,7 @@ def _llama_layer(cfg: ModelConfig):
         attn = F.attention_qkv(qkv4, Hq, Hk, seqlens=seqlens, causal=True, segment_ids=segment_ids)
         a = F.linear(attn.reshape(B, T, Hq * D), w["wo"])
         x, h = F.add_rmsnorm(x, a, w["mlp_norm"], cfg.norm_eps)
-        m = F.linear(F.linear_swiglu(h, w["w_gu"]), w["w_down"])     # SwiGLU rides in the gate/up GEMM's epilogue
+        m = F.mlp_swiglu(h, w["w_gu"], w["w_down"])     # both SwiGLU passes ride in GEMM epilogues (fwd: gate/up, bwd: down dgrad)
         return x, m
 
     return fn

@@ -444,6 +444,69 @@ class _LinearSwiGLU(Function):
         return dx, dw
 
 
+class _MLPSwiGLU(Function):
+    """The whole gated MLP ``(silu(x Wg^T) * (x Wu^T)) Wd^T`` as one autograd node, so that both SwiGLU passes ride in GEMM
+    epilogues: forward as in :class:`_LinearSwiGLU`; backward, the dgrad of the down projection emits d(gate) | d(up)
+    directly (``dla_gemm_swiglu_bwd_bf16``) — d(act) never reaches memory — followed by the usual dgrad / wgrad GEMMs."""
+
+    @staticmethod
+    def forward(ctx, x, w_gu, w_down):
+        x2 = _c(x.reshape(-1, x.shape[-1]))
+        M, K = x2.shape
+        F2 = w_gu.shape[0]
+        need_bwd = any(ctx.needs_input_grad)
+        act = torch.empty(M, F2 // 2, dtype=BF16, device=x.device)
+        gu = torch.empty(M, F2, dtype=BF16, device=x.device) if need_bwd else None
+        N.call("dla_gemm_swiglu_bf16", N.ptr(x2), N.ptr(w_gu), N.ptr(gu), N.ptr(act), M, F2 // 2, K, x2.stride(0), w_gu.stride(0),
+               F2, F2 // 2, _s(x))
+        y = gemm(act, w_down)
+        if need_bwd:
+            ctx.save_for_backward(x2, w_gu, w_down, gu, act)
+        ctx.wrefs = (w_gu, w_down)
+        ctx.xshape = x.shape
+        return y.view(*x.shape[:-1], w_down.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w_gu, w_down, gu, act = ctx.saved_tensors
+        dy2 = _c(dy.reshape(-1, dy.shape[-1]))
+        M, H = dy2.shape
+        Fh = act.shape[1]
+        dx = dwg = dwd = None
+        if ctx.needs_input_grad[2]:
+            slot, acc = _slot_gemm(ctx.wrefs[1])
+            if slot is not None:
+                gemm(dy2, act, a_mn=True, b_mn=True, out=slot, accumulate=acc)
+            else:
+                dwd = gemm(dy2, act, a_mn=True, b_mn=True)
+        dgu = torch.empty_like(gu)
+        N.call("dla_gemm_swiglu_bwd_bf16", N.ptr(dy2), N.ptr(w_down), N.ptr(gu), N.ptr(dgu), M, Fh, H, dy2.stride(0),
+               w_down.stride(0), gu.stride(0), dgu.stride(0), _s(dy2))
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dgu, w_gu, b_mn=True).view(ctx.xshape)
+        if ctx.needs_input_grad[1]:
+            slot, acc = _slot_gemm(ctx.wrefs[0])
+            if slot is not None:
+                gemm(dgu, x2, a_mn=True, b_mn=True, out=slot, accumulate=acc)
+            else:
+                dwg = gemm(dgu, x2, a_mn=True, b_mn=True)
+        return dx, dwg, dwd
+
+
+def mlp_swiglu(x: torch.Tensor, w_gu: torch.Tensor, w_down: torch.Tensor) -> torch.Tensor:
+    """``linear(swiglu(linear(x, w_gu)), w_down)``.  When the shapes suit the 2-CTA kernel both SwiGLU passes are GEMM
+    epilogues (:class:`_MLPSwiGLU`); otherwise the composition of the separate ops."""
+    F2, K = w_gu.shape
+    M = x.numel() // x.shape[-1]
+    ok = (x.is_cuda and FUSE_SWIGLU[0] and x.dtype == BF16 and w_gu.dtype == BF16 and w_down.dtype == BF16 and F2 % 256 == 0
+          and M >= 256 and K % 8 == 0 and w_down.shape[0] % 8 == 0 and ((M + 255) // 256) * (F2 // 256) >= 74
+          and all(w.stride(1) == 1 and w.stride(0) % 8 == 0 and w.data_ptr() % 16 == 0 for w in (w_gu, w_down))
+          and all(getattr(w, "_ag", None) is None or w._ag.done for w in (w_gu, w_down)))
+    if not ok:
+        return linear(linear_swiglu(x, w_gu), w_down)
+    return _MLPSwiGLU.apply(x, w_gu, w_down)
+
+
 FUSE_SWIGLU = [True]        # A/B switch (tests, DLA_FUSE_SWIGLU=0)
 
 

@@ -44,6 +44,7 @@ _SIGNATURES = {
     "dla_gemm_bf16": [P, P, P, I, I, I, I64, I64, I64, I, I, I, I, P],
     "dla_gemm_set_variant": [I],
     "dla_gemm_swiglu_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],
+    "dla_gemm_swiglu_bwd_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],
     "dla_set_device": [I],
     "dla_lmhead_logprob": [P, P, P, I, I, I, I64, I64, P, P, P, P],
     "dla_lmhead_logprob_keep": [P, P, P, I, I, I, I64, I64, P, P, P, P, I64, P],

@@ -143,6 +143,11 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
  * otherwise: run dla_gemm_bf16 + dla_swiglu_fwd).  R: the HF Llama MLP under R/src/training/train_dpo.py:32 (K1 + K5). */
 int dla_gemm_swiglu_bf16(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda,
                          int64_t ldb, int64_t ldgu, int64_t ldact, void* stream);
+/* Backward counterpart: dGU[M, 2F] = d[gate | up] from dY[M, H] (gradient of the down projection's output), the down
+ * weight Wdown[H, F] and the saved GU[M, 2F]: the dgrad GEMM dY Wdown whose epilogue applies the SwiGLU backward, so
+ * d(act) never reaches memory.  Needs M >= 256, F % 64 == 0 (DLA_E_UNSUPP otherwise: dla_gemm_bf16 + dla_swiglu_bwd). */
+int dla_gemm_swiglu_bwd_bf16(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H,
+                             int64_t lddy, int64_t ldw, int64_t ldgu, int64_t lddgu, void* stream);
 /* 0 = auto, 1 = 1-CTA 128x256, 2 = 2-CTA pair 256x256 (debug / benchmarking switch). */
 int dla_gemm_set_variant(int variant);
 

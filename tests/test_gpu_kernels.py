@@ -710,3 +710,25 @@ def test_lm_head_logprob_with_kept_logits(native_lib):
     # summation order differs: a few logits round the other way (1 bf16 ulp), nothing more
     _rel(res[True][2], res[False][2], 8e-3, what="dh kept vs recomputed")
     _rel(res[True][3], res[False][3], 8e-3, what="dW kept vs recomputed")
+
+
+@pytest.mark.parametrize("M,F_,K", [(2048, 1280, 512), (2304, 2048, 1024)])
+def test_gated_mlp_with_both_swiglu_passes_in_gemm_epilogues(native_lib, M, F_, K):
+    """``F.mlp_swiglu``: forward SwiGLU in the gate/up epilogue, backward SwiGLU in the down-projection dgrad's epilogue
+    (csrc/gemm2.cu kFuse = 2) against the fp32 autograd composition."""
+    torch.manual_seed(61)
+    x = _rand(M, K, scale=0.5)
+    wg = _rand(2 * F_, K, scale=K ** -0.5)
+    wd = _rand(K, F_, scale=F_ ** -0.5)
+    xa, wga, wda = (t.clone().requires_grad_() for t in (x, wg, wd))
+    y = F.mlp_swiglu(xa, wga, wda)
+    g = _rand(M, K, scale=0.1)
+    y.backward(g)
+    xr, wgr, wdr = (t.float().requires_grad_() for t in (x, wg, wd))
+    gu = xr @ wgr.t()
+    yr = (torch.nn.functional.silu(gu[:, :F_]) * gu[:, F_:]) @ wdr.t()
+    yr.backward(g.float())
+    _rel(y, yr, 8e-3, what="mlp fwd")
+    _rel(xa.grad, xr.grad, 1.5e-2, what="mlp dx")
+    _rel(wga.grad, wgr.grad, 1.5e-2, what="mlp dW_gu")
+    _rel(wda.grad, wdr.grad, 1.5e-2, what="mlp dW_down")
