@@ -724,6 +724,7 @@ int dla_attn_fwd_seg(const void* q, const void* k, const void* v, void* o, float
   p.B = B; p.T = T; p.Hq = Hq; p.Hk = Hk; p.D = D; p.scale = scale; p.causal = causal; p.seqlens = seqlens;
   p.seg_start = seg_start;
   p.o = (bf16*)o; p.o_sb = o_sb; p.o_st = o_st; p.o_sh = o_sh; p.lse = lse;
+  p.debug_flags = g_fwd_variant >= 16 ? (g_fwd_variant & 15) : 0;     // A/B switches of the ping-pong kernel (bit 2: two-pass softmax only)
   dim3 grid((T + BQ - 1) / BQ, Hq, B);
   cudaStream_t s = (cudaStream_t)stream;
   if (g_fwd_variant == 3) return attn_fwd3_dispatch(tmQ, tmK, tmV, p, s);     // early-S ping-pong kernel (attn_fwd3.cu)

@@ -200,6 +200,59 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         limit = lim - kv0;
         lo = row_lo - kv0;
       }
+      float s4[4] = {0.f, 0.f, 0.f, 0.f};
+      bool done = false;
+      // ---- optimistic single pass (every kv tile after the first): exponentiate against the CURRENT reference while the
+      // row maximum is tracked on the side; the next 32-column chunk is requested from TMEM before the current one is
+      // processed, so the TMEM latency hides under the MUFU work.  P stays in registers until the maximum is known: if no
+      // row of the warp moved by more than the rescale threshold (the usual case — the reference only has to be within 2^8)
+      // it is committed as is; otherwise nothing was stored, S is still intact, and the two-pass path below redoes the tile.
+      if (j > 0 && !__any_sync(0xffffffffu, m_ref == -INFINITY) && !(p.debug_flags & 4)) {
+        const float neg_m = -m_ref;
+        uint32_t pk[64];
+        uint32_t v[2][32];
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        tc::tmem_ld_32x32(tS, v[0]);
+        tc::tmem_ld_wait_for(v[0]);
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          if (ch < 3) tc::tmem_ld_32x32(tS + (ch + 1) * 32, v[(ch + 1) & 1]);
+          const uint32_t* cur = v[ch & 1];
+          if (!need_mask) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const float a0 = __uint_as_float(cur[i]), a1 = __uint_as_float(cur[i + 1]);
+              mx4[(i >> 1) & 3] = fmaxf(mx4[(i >> 1) & 3], fmaxf(a0, a1));
+              const float p0 = ex2_approx(fmaf(a0, scale2, neg_m));
+              const float p1 = ex2_approx(fmaf(a1, scale2, neg_m));
+              s4[(i >> 1) & 3] += p0 + p1;
+              pk[ch * 16 + (i >> 1)] = pack_bf16x2(p0, p1);
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) {
+              const int c = ch * 32 + i;
+              const bool ok0 = c < limit && c >= lo, ok1 = c + 1 < limit && c + 1 >= lo;
+              const float a0 = ok0 ? __uint_as_float(cur[i]) : -INFINITY, a1 = ok1 ? __uint_as_float(cur[i + 1]) : -INFINITY;
+              mx4[(i >> 1) & 3] = fmaxf(mx4[(i >> 1) & 3], fmaxf(a0, a1));
+              const float p0 = ok0 ? ex2_approx(fmaf(a0, scale2, neg_m)) : 0.f;
+              const float p1 = ok1 ? ex2_approx(fmaf(a1, scale2, neg_m)) : 0.f;
+              s4[(i >> 1) & 3] += p0 + p1;
+              pk[ch * 16 + (i >> 1)] = pack_bf16x2(p0, p1);
+            }
+          }
+          if (ch < 3) tc::tmem_ld_wait_for(v[(ch + 1) & 1]);
+        }
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * scale2;
+        if (!__any_sync(0xffffffffu, mx > m_ref + kRescaleThreshold)) {
+          tc::tmem_st_32x32(tS, pk);
+          tc::tmem_st_32x32(tS + 32, pk + 32);
+          done = true;
+        } else {
+          s4[0] = s4[1] = s4[2] = s4[3] = 0.f;
+        }
+      }
+      if (!done) {
       // ---- pass 1: row maximum.  The four 32-column loads are in flight together (one wait), and four
       // independent max chains keep the FMNMX latency off the critical path of this lone warp.
       float mx;
@@ -240,7 +293,6 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
       // ---- pass 2: P = exp2(S * scale2 - m_ref) -> bf16 pairs -> TMEM columns [0, 64) of S_x.
       // Both 64-column halves are requested up front; P of half 0 overwrites S[0,32) (already in registers),
       // P of half 1 overwrites S[32,64).
-      float s4[4] = {0.f, 0.f, 0.f, 0.f};
       {
         uint32_t v[128];
 #pragma unroll
@@ -269,6 +321,7 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
           }
           tc::tmem_st_32x32(tS + half * 32, pk);
         }
+      }
       }
       const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
       tc::tmem_st_wait();

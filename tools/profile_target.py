@@ -27,6 +27,11 @@ elif what in ("attn_fwd", "attn_bwd"):
         o = F.attention(q, k, v)
         if what == "attn_bwd":
             torch.autograd.grad(o, qkv, r(B, T, Hq, D))
+elif what == "attn_fwd_4k":
+    B, T, Hq, Hk, D = 2, 4096, 32, 8, 128
+    qkv = r(B, T, Hq + 2 * Hk, D)
+    for _ in range(3):
+        o = F.attention_qkv(qkv, Hq, Hk)
 elif what == "skinny":
     x, w = r(8, 4096), r(28672, 4096)
     for _ in range(3):
