@@ -28,6 +28,11 @@ namespace attn {
 
 constexpr int kFwd2Threads = 320;
 constexpr float kRescaleThreshold = 8.f;     // log2 units
+// Half of the exponentials of unmasked tiles on the FMA pipe (ex2_poly) instead of the MUFU.  Measured on B200 and left OFF:
+// 390 vs 327 us at B=2 T=4096, 672 vs 537 us at T=8192 — with two softmax warps per scheduler the loop is bound by
+// instruction issue and dependency latency (issue active 36 %, stalls: long scoreboard, fixed-latency wait), not by MUFU
+// throughput, so nine extra FMA/ALU instructions per element cost more than the MUFU slot they free.
+constexpr bool kPolyExp = false;
 
 template <int HD>
 __global__ void __launch_bounds__(kFwd2Threads, 1)
@@ -223,8 +228,10 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             for (int i = 0; i < 32; i += 2) {
               const float a0 = __uint_as_float(cur[i]), a1 = __uint_as_float(cur[i + 1]);
               mx4[(i >> 1) & 3] = fmaxf(mx4[(i >> 1) & 3], fmaxf(a0, a1));
-              const float p0 = ex2_approx(fmaf(a0, scale2, neg_m));
-              const float p1 = ex2_approx(fmaf(a1, scale2, neg_m));
+              // every other pair is exponentiated on the FMA pipe instead of the MUFU (see ex2_poly)
+              const bool poly = kPolyExp && ((i >> 1) & 1);
+              const float p0 = poly ? ex2_poly(fmaf(a0, scale2, neg_m)) : ex2_approx(fmaf(a0, scale2, neg_m));
+              const float p1 = poly ? ex2_poly(fmaf(a1, scale2, neg_m)) : ex2_approx(fmaf(a1, scale2, neg_m));
               s4[(i >> 1) & 3] += p0 + p1;
               pk[ch * 16 + (i >> 1)] = pack_bf16x2(p0, p1);
             }
