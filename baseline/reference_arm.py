@@ -19,7 +19,7 @@ import os
 import sys
 import types
 from pathlib import Path
-from typing import Any, Dict, Tuple
+from typing import Any, Dict
 
 import torch
 import torch.distributed as dist

@@ -13,8 +13,6 @@ from __future__ import annotations
 
 from typing import Any, Dict, List
 
-import torch
-
 from dla_b200.algo import distill_step
 from dla_b200.cli.common import TrainLoop, parse_args, setup
 from dla_b200.data import TeacherRolloutDataset

@@ -30,7 +30,6 @@ from dla_b200.models.factory import build_reward_model, load_causal_lm
 from dla_b200.models.reward import ValueHead, value_head_unit
 from dla_b200.models.config import resolve_model_config
 from dla_b200.ops import functional as F
-from dla_b200.ops import reference as R
 from dla_b200.optim import AdamWConfig
 from dla_b200.rollout import Generator, decode_responses, splice_separator
 

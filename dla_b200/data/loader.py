@@ -8,7 +8,7 @@ overlaps the previous step's compute.
 """
 from __future__ import annotations
 
-from typing import Any, Callable, Dict, Iterable, Iterator, Optional
+from typing import Any, Callable, Iterable, Iterator, Optional
 
 import torch
 from torch.utils.data import DataLoader, Dataset

@@ -11,7 +11,6 @@ holds safetensors (no hub access).
 from __future__ import annotations
 
 from dataclasses import dataclass
-from pathlib import Path
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -20,7 +19,7 @@ from dla_b200.config import HardwarePlan
 from dla_b200.data.tokenizer import load_tokenizer
 from dla_b200.models.config import ModelConfig, resolve_model_config
 from dla_b200.models.io import has_pretrained_weights
-from dla_b200.models.reward import RewardModel, reward_units, value_head_unit
+from dla_b200.models.reward import RewardModel, reward_units
 from dla_b200.models.transformer import CausalLM, build_units
 from dla_b200.parallel.engine import Engine
 from dla_b200.parallel.pg import DistContext

@@ -7,8 +7,7 @@ eager PyTorch (the CPU path exists only for tensors that live on the CPU).
 from __future__ import annotations
 
 import ctypes
-import os
-from ctypes import c_float, c_int, c_int32, c_int64, c_longlong, c_size_t, c_uint32, c_uint64, c_void_p
+from ctypes import c_float, c_int, c_int64, c_longlong, c_size_t, c_uint32, c_uint64, c_void_p
 from pathlib import Path
 from typing import Dict, Optional, Tuple
 

@@ -14,10 +14,9 @@ NCCL equivalents replaced: ``reduce_scatter_tensor`` + ``all_gather_into_tensor`
 from __future__ import annotations
 
 import os
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, Optional, Tuple
 
 import torch
-import torch.distributed as dist
 
 from dla_b200.ops import native as N
 from dla_b200.parallel.pg import DistContext

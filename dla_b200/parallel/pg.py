@@ -12,7 +12,7 @@ from __future__ import annotations
 import datetime
 import os
 from dataclasses import dataclass
-from typing import Any, List, Optional
+from typing import Any, Optional
 
 import torch
 import torch.distributed as dist

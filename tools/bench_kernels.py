@@ -4,7 +4,6 @@ fractions against MEASURED_PEAKS.json.  Writes JSON lines to gpurun_out/kernels.
 from __future__ import annotations
 
 import json
-import math
 import sys
 from pathlib import Path
 
