@@ -507,3 +507,50 @@ def test_watchdog_turns_a_missing_peer_into_an_exception():
     """a peer that stops taking part must not hang the others forever or let them compute on half-exchanged
     data — the flag wait is bounded by wall time and the training loop's per-step poll raises."""
     mp.spawn(_watchdog_worker, args=(2, _free_port()), nprocs=2, join=True)
+
+
+def _freeze_worker(rank, world, port, out):
+    ctx = _init(rank, world, port)
+    from dla_b200.algo import dpo_step
+    from dla_b200.config import HardwarePlan
+    from dla_b200.data.synthetic import synthetic_preference_batch
+    from dla_b200.models.factory import freeze_except_lora, load_causal_lm
+    from dla_b200.optim import AdamWConfig
+
+    res = {}
+    for comm in ("nccl", "fused"):
+        plan = HardwarePlan(sharding="zero3", comm=comm, resident_params=True)
+        pol = load_causal_lm("tiny-llama", ctx, plan, seed=21, name=f"policy_{comm}")
+        ref = load_causal_lm("tiny-llama", ctx, plan, trainable=False, gradient_checkpointing=False, seed=21, name=f"ref_{comm}")
+        info = freeze_except_lora(pol.engine, "w_down")
+        assert 0 < info["trainable_params"] < info["total_params"]
+        names = [(u.name, p.name) for u in pol.engine.units for p in u.params]
+        before = {n: pol.engine.gathered_unit(n[0])[n[1]].clone() for n in names}
+        for step in range(3):
+            full = synthetic_preference_batch(2 * world, 128, pol.config.vocab_size, seed=80 + step, ragged=True)
+            batch = {s: {k: v[rank * 2:(rank + 1) * 2].cuda() for k, v in full[s].items()} for s in full}
+            loss, _ = dpo_step(pol.model, ref.model, batch, beta=0.5)
+            loss.backward()
+            pol.engine.finish_backward()
+            pol.engine.optimizer_step(AdamWConfig(lr=1e-3, weight_decay=0.1, max_grad_norm=1.0), grad_divisor=float(world))
+        after = {n: pol.engine.gathered_unit(n[0])[n[1]] for n in names}
+        for n in names:
+            if "w_down" in f"{n[0]}.{n[1]}":
+                assert not torch.equal(before[n], after[n]), (comm, n)
+            else:
+                assert torch.equal(before[n], after[n]), (comm, n, "a frozen parameter moved")
+        res[comm] = (torch.cat([after[n].reshape(-1).float() for n in names]).cpu(), float(pol.engine.last_grad_norm))
+    if rank == 0:
+        torch.save(res, out)
+    ctx.barrier()
+
+
+def test_freeze_except_on_the_sharded_engines(tmp_path):
+    """Substring freezing (P15) on ZeRO-3 with both engines: frozen parameters stay bit-identical on every rank (no weight
+    decay, no update), the trainable ones move, the clipped norm counts trainable gradients only, fused == NCCL."""
+    out = tmp_path / "freeze.pt"
+    mp.spawn(_freeze_worker, args=(2, _free_port(), str(out)), nprocs=2, join=True)
+    res = torch.load(out)
+    (pn, gn), (pf, gf) = res["nccl"], res["fused"]
+    assert gn == pytest.approx(gf, rel=3e-2)
+    assert float((pn - pf).norm() / pn.norm()) < 3e-3
