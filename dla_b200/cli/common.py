@@ -72,6 +72,13 @@ class TrainLoop:
                                 nvtx=bool(log_cfg.get("nvtx", False)))
         self.reward_bin = reward_bin
         self.tokens_fn, self.flops_per_token = tokens_fn, flops_per_token
+        # optional torch.profiler window: logging.torch_profiler: {start_step: N, steps: K, dir: path}
+        # records K micro-steps starting at global step N on every rank, writes a Chrome trace per rank and, on rank 0,
+        # the per-kernel table; outside the window nothing is hooked
+        tp = log_cfg.get("torch_profiler") or {}
+        self._prof_cfg = {"start": int(tp.get("start_step", 0)), "steps": int(tp.get("steps", 0)),
+                          "dir": str(tp.get("dir") or Path(self.log_dir) / "profiler")} if tp else None
+        self._prof = None
         self._tok_since, self._t_since = 0, time.perf_counter()
         self._ev0 = None
         self.sampler_state: Dict[str, Any] = {}
@@ -95,6 +102,7 @@ class TrainLoop:
 
     def micro_step(self, loss_fn: Callable[[], torch.Tensor], batch: Any = None) -> torch.Tensor:
         """forward + backward of one micro-batch; optimizer update on accumulation boundaries."""
+        self._profiler_window()
         boundary = (self.micro_steps + 1) % self.accum == 0
         self.engine.sync_grads = boundary
         with self.timer("fwd"):
@@ -115,6 +123,29 @@ class TrainLoop:
         if self.tokens_fn is not None and batch is not None:
             self._tok_since += int(self.tokens_fn(batch))
         return loss.detach()
+
+    def _profiler_window(self) -> None:
+        pc = self._prof_cfg
+        if not pc or pc["steps"] <= 0:
+            return
+        if self._prof is None and self.global_step == pc["start"]:
+            acts = [torch.profiler.ProfilerActivity.CPU]
+            if self.ctx.device.type == "cuda":
+                acts.append(torch.profiler.ProfilerActivity.CUDA)
+            self._prof = torch.profiler.profile(activities=acts)
+            self._prof.__enter__()
+        elif self._prof is not None and self.global_step >= pc["start"] + pc["steps"]:
+            if self.ctx.device.type == "cuda":
+                torch.cuda.synchronize(self.ctx.device)
+            self._prof.__exit__(None, None, None)
+            out = Path(pc["dir"])
+            out.mkdir(parents=True, exist_ok=True)
+            self._prof.export_chrome_trace(str(out / f"trace_rank{self.ctx.rank}_step{pc['start']}.json"))
+            if self.ctx.is_main:
+                key = "cuda_time_total" if self.ctx.device.type == "cuda" else "cpu_time_total"
+                (out / f"kernels_step{pc['start']}.txt").write_text(self._prof.key_averages().table(sort_by=key, row_limit=40))
+                self.ctx.print0(f"[{self.phase}] torch.profiler window of {pc['steps']} step(s) written to {out}")
+            self._prof, self._prof_cfg = None, None
 
     def _size_kept_activations(self) -> None:
         """``hardware.keep_activations``: once the first update has shown the allocator's steady state, spend the free
@@ -190,6 +221,11 @@ class TrainLoop:
         return self.global_step >= self.total_steps
 
     def finish(self, message: str, sampler: Any = None) -> None:
+        self._profiler_window()      # close a window that reaches the end of training
+        if self._prof is not None:
+            self._prof_cfg["steps"] = 0
+            self._prof.__exit__(None, None, None)
+            self._prof = None
         self.save("final", sampler)
         self.ckpt.wait()            # a background writer (logging.async_checkpoint) must finish before the process exits
         self.logger.close()

@@ -63,8 +63,10 @@ def test_sft_with_sequence_packing(work, device):
         "data": {"source": "local", "train_path": str(work / "sft.jsonl"), "num_workers": 0, "packing": True},
         "optimization": {"micro_batch_size": 6, "learning_rate": 1e-3, "warmup_steps": 1, "max_train_steps": 3},
         "logging": _log(d, "sft_pack", save_every_steps=0), "hardware": {"device": device}})
-    out = _run("dla_b200.cli.train_sft", "--config", cfg)
-    assert "Training complete" in out
+    out = _run("dla_b200.cli.train_sft", "--config", cfg, "--override", "logging.torch_profiler={start_step: 1, steps: 1}")
+    assert "Training complete" in out and "torch.profiler window" in out
+    prof_dir = d / "logs" / "sft_pack" / "profiler"
+    assert (prof_dir / "trace_rank0_step1.json").exists() and (prof_dir / "kernels_step1.txt").exists()
     metrics = [json.loads(l) for l in (d / "logs" / "sft_pack" / "metrics.jsonl").read_text().splitlines()]
     losses = [m["train/loss"] for m in metrics if "train/loss" in m]
     assert losses and all(l == l and l < 20 for l in losses)

@@ -264,3 +264,32 @@ def test_gpt2_small_dpo_cli_gloo_world2(tmp_path):
     lines = [json.loads(l) for l in (tmp_path / "logs" / "metrics.jsonl").read_text().splitlines()]
     assert any("train/loss" in l for l in lines)
     assert (tmp_path / "ck" / "latest" / "model.safetensors").exists()
+
+
+@pytest.mark.timeout(120)
+def test_launcher_takes_ranks_down_and_restarts_from_latest(tmp_path):
+    """a rank that dies must not leave its peers hanging, and ``--max-restarts`` relaunches the job with
+    ``--resume latest`` on a fresh rendezvous port."""
+    import subprocess
+    import time
+
+    # the stand-in training script is importable under a name of its own (a `tests` package elsewhere on the path would
+    # shadow `-m tests.launch_crash_helper`)
+    (tmp_path / "dla_launch_crash_helper.py").write_text((ROOT / "tests" / "launch_crash_helper.py").read_text())
+    env = dict(os.environ, PYTHONPATH=f"{ROOT}{os.pathsep}{tmp_path}", CUDA_VISIBLE_DEVICES="")
+    marker = tmp_path / "marker"
+    t0 = time.monotonic()
+    res = subprocess.run([sys.executable, "-m", "dla_b200.cli.launch", "--nproc", "2", "--cpu", "--port", str(_free_port()),
+                          "--max-restarts", "1", "-m", "dla_launch_crash_helper", "--marker", str(marker)],
+                         cwd=ROOT, env=env, capture_output=True, text=True, timeout=100)
+    assert res.returncode == 0, res.stdout + res.stderr
+    assert time.monotonic() - t0 < 45, "the surviving rank was not taken down promptly"
+    assert "restarting 2 rank(s) with --resume latest" in res.stdout
+    ports = {(tmp_path / f"done_{r}").read_text() for r in range(2)}
+    assert len(ports) == 1
+    # without restarts the failing rank's exit code propagates
+    marker.unlink()
+    res = subprocess.run([sys.executable, "-m", "dla_b200.cli.launch", "--nproc", "2", "--cpu", "--port", str(_free_port()),
+                          "-m", "dla_launch_crash_helper", "--marker", str(marker)],
+                         cwd=ROOT, env=env, capture_output=True, text=True, timeout=100)
+    assert res.returncode == 7
