@@ -70,6 +70,9 @@ def llama_hf_config(name: str):
         "llama3-8b": dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=32,
                           num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=8192,
                           rope_theta=500000.0, rms_norm_eps=1e-5),
+        "llama3-70b": dict(vocab_size=128256, hidden_size=8192, intermediate_size=28672, num_hidden_layers=80,
+                           num_attention_heads=64, num_key_value_heads=8, max_position_embeddings=8192,
+                           rope_theta=500000.0, rms_norm_eps=1e-5),
         "llama-1b": dict(vocab_size=32000, hidden_size=2048, intermediate_size=5632, num_hidden_layers=16,
                          num_attention_heads=16, num_key_value_heads=4, max_position_embeddings=4096,
                          rope_theta=500000.0, rms_norm_eps=1e-5),
@@ -80,6 +83,39 @@ def llama_hf_config(name: str):
     cfg = LlamaConfig(**presets[name], tie_word_embeddings=False, attn_implementation="sdpa")
     cfg.use_cache = False
     return cfg
+
+
+def param_bytes(cfg) -> int:
+    """bf16 bytes of one LlamaForCausalLM of this config (untied head)."""
+    h, f, L, v = cfg.hidden_size, cfg.intermediate_size, cfg.num_hidden_layers, cfg.vocab_size
+    kv = h // cfg.num_attention_heads * cfg.num_key_value_heads
+    per_layer = h * (h + 2 * kv) + h * h + 3 * h * f + 2 * h
+    return 2 * (L * per_layer + 2 * v * h + h)
+
+
+def build_on_meta(cfg):
+    """The module tree with no storage behind it: what accelerate/DeepSpeed ZeRO-3 do for a model that does not
+    fit one GPU (``zero3_init_flag``), here with torch's meta device."""
+    from transformers import LlamaForCausalLM
+
+    with torch.device("meta"):
+        return LlamaForCausalLM(cfg).to(torch.bfloat16)
+
+
+@torch.no_grad()
+def materialize_sharded(model, cfg, device: torch.device, seed: int) -> None:
+    """Allocate only this rank's shards and fill them with HF's initialisation (normal(0, initializer_range)
+    for matrices and embeddings, ones for the norm gains); rebuild the rotary tables the meta device dropped."""
+    model.to_empty(device=device)
+    gen = torch.Generator(device=device).manual_seed(seed)
+    for _, p in model.named_parameters():
+        local = p.to_local() if hasattr(p, "to_local") else p
+        if p.dim() == 1:
+            local.fill_(1.0)
+        else:
+            local.normal_(0.0, cfg.initializer_range, generator=gen)
+    rot = model.model.rotary_emb
+    model.model.rotary_emb = type(rot)(config=cfg, device=device)
 
 
 class ReferenceDPO:
@@ -94,9 +130,15 @@ class ReferenceDPO:
         cfg = llama_hf_config(model_name)
         self.device, self.world, self.beta = device, world, beta
         torch.manual_seed(0)
-        with torch.device(device):
-            policy = LlamaForCausalLM(cfg).to(torch.bfloat16)
-            ref = LlamaForCausalLM(cfg).to(torch.bfloat16)
+        # two replicas that would not fit one GPU (70B) are built on the meta device and materialised shard by shard
+        hbm = torch.cuda.get_device_properties(device).total_memory if device.type == "cuda" else 1 << 62
+        self.meta_init = world > 1 and sharded and (2 * param_bytes(cfg) > 0.5 * hbm or os.environ.get("DLA_REF_META_INIT") == "1")
+        if self.meta_init:
+            policy, ref = build_on_meta(cfg), build_on_meta(cfg)
+        else:
+            with torch.device(device):
+                policy = LlamaForCausalLM(cfg).to(torch.bfloat16)
+                ref = LlamaForCausalLM(cfg).to(torch.bfloat16)
         policy.gradient_checkpointing_enable()
         policy.train()      # HF only checkpoints in train mode; Llama has no dropout so the math is unchanged
         ref.eval()
@@ -110,6 +152,10 @@ class ReferenceDPO:
                     for layer in m.model.layers:
                         fully_shard(layer)
                     fully_shard(m)
+                if self.meta_init:
+                    rank = dist.get_rank()
+                    materialize_sharded(policy, cfg, device, seed=1000 + rank)
+                    materialize_sharded(ref, cfg, device, seed=2000 + rank)
             else:
                 policy = torch.nn.parallel.DistributedDataParallel(policy, device_ids=[device.index], find_unused_parameters=False)
         self.policy, self.ref = policy, ref
@@ -202,7 +248,8 @@ class ReferenceArm:
         return 0        # none of this repo's kernels exist in this process; see ``native_so_in_process``
 
     def describe(self) -> Dict[str, Any]:
-        return {"optimizer": "torch AdamW on bf16 params", "activation_checkpointing": True}
+        return {"optimizer": "torch AdamW on bf16 params", "activation_checkpointing": True,
+                "meta_init": bool(self.runner.meta_init)}
 
     @staticmethod
     def native_so_in_process() -> bool:

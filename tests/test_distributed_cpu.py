@@ -293,3 +293,47 @@ def test_launcher_takes_ranks_down_and_restarts_from_latest(tmp_path):
                           "-m", "dla_launch_crash_helper", "--marker", str(marker)],
                          cwd=ROOT, env=env, capture_output=True, text=True, timeout=100)
     assert res.returncode == 7
+
+
+def _ref_meta_worker(rank, world, port):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port), DLA_REF_META_INIT="1")
+    import warnings
+
+    import torch.distributed as dist
+
+    sys.path.insert(0, str(ROOT))
+    from baseline import reference_arm as ra
+
+    if ra.locate() is None:
+        return
+    warnings.simplefilter("ignore")
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    runner = ra.ReferenceDPO("tiny-llama", torch.device("cpu"), world, sharded=True)
+    assert runner.meta_init
+    assert not any(p.is_meta for m in (runner.policy, runner.ref) for p in m.parameters())
+    inv = runner.policy.model.rotary_emb.inv_freq
+    assert not inv.is_meta and float(inv[0]) == 1.0 and bool(torch.isfinite(inv).all())
+    gains = [p for n, p in runner.policy.named_parameters() if n.endswith("norm.weight")]
+    assert gains and all(bool((g.to_local() == 1).all()) for g in gains)
+    vocab = ra.llama_hf_config("tiny-llama").vocab_size
+    for i in range(2):
+        loss = runner.step(ra.synthetic_preference_batch(2, 32, vocab, seed=i + 10 * rank))
+        assert bool(torch.isfinite(loss))
+    dist.destroy_process_group()
+
+
+def test_reference_arm_meta_init_shards_before_materialising():
+    """The 70B reference arm builds both replicas on the meta device, shards them with FSDP2 and only then
+    allocates; the same code path is forced here on the tiny preset over gloo."""
+    if not (ROOT / "baseline" / "_ref").exists() and not Path("/root/reference").exists():
+        pytest.skip("reference tree not present")
+    mp.spawn(_ref_meta_worker, args=(2, _free_port()), nprocs=2, join=True)
+
+
+def test_reference_arm_param_count_formula():
+    sys.path.insert(0, str(ROOT))
+    from baseline import reference_arm as ra
+
+    assert abs(ra.param_bytes(ra.llama_hf_config("llama3-8b")) / 2 - 8.03e9) < 0.01e9
+    assert abs(ra.param_bytes(ra.llama_hf_config("llama3-70b")) / 2 - 70.55e9) < 0.05e9
