@@ -14,6 +14,7 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 
@@ -126,6 +127,7 @@ struct Params {
   int store_mode;     // 0 = TMA store / reduce-add through staged smem, 1 = direct st.global from the TMEM layout
   int num_m_tiles, num_n_tiles;
   int k_splits;       // > 1: every output tile is computed by k_splits CTAs over disjoint K ranges and reduce-added (C pre-zeroed)
+  const bf16* bias;   // [N] added to every output row in the epilogue (by K slice 0 only when split); nullptr: none
   // log-prob epilogue
   const int64_t* labels;
   float2* partials;   // [num_n_tiles, M] (max, sumexp)
@@ -381,6 +383,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
 
       if constexpr (kEpi == kStore) {
+       const bf16* bias = (t / out_tiles == 0) ? p.bias : nullptr;      // split-K: slice 0 carries the bias
        if (p.store_mode == 0) {
         // TMEM -> registers -> 128B-swizzled staging rows -> TMA store (or TMA reduce-add when accumulating).
         // The output never touches the LSU path: uncoalesced per-row st.global from the TMEM layout used
@@ -399,6 +402,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             uint32_t r[32];
             tc::tmem_ld_32x32(taddr + gi * 32, r);
             tc::tmem_ld_wait();
+            if (bias != nullptr) tc::add_bias_row<32>(r, bias, col_base + gi * 32, p.N);
 #pragma unroll
             for (int c = 0; c < 8; ++c)
               *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = make_uint4(r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
@@ -407,6 +411,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             tc::tmem_ld_32x32(taddr + gi * 64, r);
             tc::tmem_ld_32x32(taddr + gi * 64 + 32, r + 32);
             tc::tmem_ld_wait();
+            if (bias != nullptr) tc::add_bias_row<64>(r, bias, col_base + gi * 64, p.N);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
               uint4 v;
@@ -435,6 +440,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
           tc::tmem_ld_32x32(taddr + ch * 32, r);
           tc::tmem_ld_wait();
           const int col0 = col_base + ch * 32;
+          if (bias != nullptr && col0 < p.N) tc::add_bias_row<32>(r, bias, col0, p.N);
           if (row < p.M && col0 < p.N) {
             const bool full = (col0 + 32 <= p.N);
             if (p.c_fp32) {
@@ -639,8 +645,8 @@ static int build_maps(CUtensorMap* tmA, CUtensorMap* tmB, const void* A, const v
 }  // namespace dla
 
 namespace dla {
-int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
-                   int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream);
+int gemm2_dispatch(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                   int64_t ldc, int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream);
 int gemm2_swiglu_dispatch(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda, int64_t ldb,
                           int64_t ldgu, int64_t ldact, cudaStream_t stream);
 int gemm2_swiglu_bwd_dispatch(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H, int64_t lddy,
@@ -650,6 +656,9 @@ void gemm2_set_tail_split(int on);
 
 using namespace dla;
 using namespace dla::gemm;
+
+static int gemm_entry(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                      int64_t ldc, int a_mn_major, int b_mn_major, int c_fp32, int accumulate, void* stream);
 
 extern "C" {
 
@@ -664,6 +673,19 @@ int dla_gemm_set_variant(int variant) {
 
 int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
                   int a_mn_major, int b_mn_major, int c_fp32, int accumulate, void* stream) {
+  return gemm_entry(A, B, C, nullptr, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, c_fp32, accumulate, stream);
+}
+
+int dla_gemm_bias_bf16(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                       int64_t ldc, int c_fp32, void* stream) {
+  DLA_REQUIRE(bias != nullptr, DLA_E_BADARG, "gemm_bias: bias is required (use dla_gemm_bf16 without one)");
+  return gemm_entry(A, B, C, bias, M, N, K, lda, ldb, ldc, 0, 0, c_fp32, 0, stream);
+}
+
+}  // extern "C"
+
+static int gemm_entry(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                      int64_t ldc, int a_mn_major, int b_mn_major, int c_fp32, int accumulate, void* stream) {
   if (int rc_ = ::dla::ensure_device()) return rc_;
   DLA_REQUIRE(M > 0 && N > 0 && K > 0, DLA_E_BADARG, "gemm: empty problem %dx%dx%d", M, N, K);
   DLA_REQUIRE(K % 8 == 0, DLA_E_BADARG, "gemm: K=%d must be a multiple of 8", K);
@@ -674,6 +696,7 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   if (rc) return rc;
   Params p{};
   p.M = M; p.N = N; p.K = K; p.C = C; p.ldc = ldc; p.c_fp32 = c_fp32; p.accumulate = accumulate;
+  p.bias = reinterpret_cast<const bf16*>(bias);
   p.num_m_tiles = (M + BM - 1) / BM;
   p.num_n_tiles = (N + BN - 1) / BN;
   const int64_t esz = c_fp32 ? 4 : 2;
@@ -687,7 +710,7 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
     return e != nullptr ? atoi(e) : 32768;
   }();
   if (tma_ok && (g_variant == 2 || (g_variant == 0 && g_auto_2cta && tiles2 >= kNumSMs / 2 && M >= 256 && K <= max_k_2cta)))
-    return gemm2_dispatch(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, c_fp32, accumulate, (cudaStream_t)stream);
+    return gemm2_dispatch(A, B, C, bias, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, c_fp32, accumulate, (cudaStream_t)stream);
   CUtensorMap tmC{};
   if (tma_ok) {
     rc = make_tmap_2d(&tmC, C, c_fp32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (int)esz, (uint64_t)N,
@@ -717,6 +740,8 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, in
   if (a_mn_major && !b_mn_major) return launch<true, false, kStore>(tmA, tmB, tmC, p, s);
   return launch<true, true, kStore>(tmA, tmB, tmC, p, s);
 }
+
+extern "C" {
 
 int dla_gemm_swiglu_bf16(const void* A, const void* B, void* GU, void* ACT, int M, int F, int K, int64_t lda, int64_t ldb,
                          int64_t ldgu, int64_t ldact, void* stream) {

@@ -22,6 +22,8 @@
 // problem has at least one full wave of 256x256 tiles (see gemm.cu) or forced with dla_gemm_set_variant(2).
 #include <math.h>
 
+#include <atomic>
+
 #include "tc_common.cuh"
 
 namespace dla {
@@ -54,6 +56,7 @@ struct Params {
   int store_gu;     // kFuse 1: also store gate / up (bf16) through tmC for the backward
   const bf16* gu;   // kFuse 2: saved [M, 2F] gate | up
   int64_t ldgu;
+  const bf16* bias; // kFuse 0: [N] added to every output row (forward linears with a bias; never with accumulate / tail split)
 };
 
 // work item w -> (tile, K-block range).  Items below `full` are whole tiles; the rest are K slices of the tail tiles,
@@ -358,6 +361,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           uint32_t r[32];
           tc::tmem_ld_32x32(taddr + gi * 32, r);
           tc::tmem_ld_wait();
+          if (p.bias != nullptr) tc::add_bias_row<32>(r, p.bias, col_base + gi * 32, p.N);
 #pragma unroll
           for (int c = 0; c < 8; ++c)
             *reinterpret_cast<uint4*>(myrow + ((c ^ (lane & 7)) << 4)) = make_uint4(r[4 * c], r[4 * c + 1], r[4 * c + 2], r[4 * c + 3]);
@@ -366,6 +370,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           tc::tmem_ld_32x32(taddr + gi * 64, r);
           tc::tmem_ld_32x32(taddr + gi * 64 + 32, r + 32);
           tc::tmem_ld_wait();
+          if (p.bias != nullptr) tc::add_bias_row<64>(r, p.bias, col_base + gi * 64, p.N);
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
             uint4 v;
@@ -429,10 +434,13 @@ template <bool kAMN, bool kBMN, int kFuse = 0>
 static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC, const CUtensorMap& tmD, const Params& p,
                   cudaStream_t stream) {
   auto kern = gemm2_kernel<kAMN, kBMN, kFuse>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_devices{0};      // per-device function attribute, as in gemm.cu
+  int dev = 0;
+  DLA_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ULL << (dev & 63);
+  if (!(attr_devices.load(std::memory_order_relaxed) & bit)) {
     DLA_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    attr_set = true;
+    attr_devices.fetch_or(bit, std::memory_order_relaxed);
   }
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
   const int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
@@ -446,8 +454,8 @@ static int g_tail_split = 1;
 void gemm2_set_tail_split(int on) { g_tail_split = on; }
 
 // called from dla_gemm_bf16 (gemm.cu)
-int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
-                   int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream) {
+int gemm2_dispatch(const void* A, const void* B, void* C, const void* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                   int64_t ldc, int a_mn, int b_mn, int c_fp32, int accumulate, cudaStream_t stream) {
   using namespace gemm2;
   CUtensorMap tmA, tmB, tmC;
   int rc;
@@ -463,6 +471,7 @@ int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, i
   if (rc) return rc;
   Params p{};
   p.M = M; p.N = N; p.K = K; p.c_fp32 = c_fp32; p.accumulate = accumulate;
+  p.bias = reinterpret_cast<const bf16*>(bias);
   p.num_m_tiles = (M + 255) / 256;
   p.num_n_tiles = (N + BN - 1) / BN;
   // last partial wave: if it fills at most half of the clusters, split its tiles along K so the wave is full
@@ -470,7 +479,7 @@ int gemm2_dispatch(const void* A, const void* B, void* C, int M, int N, int K, i
   const int R = T > Cn ? T % Cn : 0;
   // Only where the slices add into storage that accumulates anyway (gradient buckets, fp32 outputs): a bf16 activation
   // tile keeps its single fp32-accumulated rounding, identical to the unsplit kernel.
-  if (g_tail_split && (accumulate || c_fp32) && R > 0 && 2 * R <= Cn && num_kb >= 16) {
+  if (g_tail_split && bias == nullptr && (accumulate || c_fp32) && R > 0 && 2 * R <= Cn && num_kb >= 16) {
     int sp = Cn / R;
     if (sp > 8) sp = 8;
     if (sp > num_kb / 8) sp = num_kb / 8;

@@ -206,6 +206,29 @@ __device__ __forceinline__ void tmem_ld_wait_for(uint32_t* r) {
                : "memory");
 }
 
+// Epilogue bias: r holds kN consecutive fp32 accumulator columns (bit patterns) of one row starting at column col0;
+// adds bias[col0 .. col0 + kN) (bf16, one 16-byte broadcast load per 8 columns, scalar loads at the ragged edge).
+template <int kN>
+__device__ __forceinline__ void add_bias_row(uint32_t (&r)[kN], const __nv_bfloat16* __restrict__ bias, int col0, int N) {
+#pragma unroll
+  for (int j = 0; j < kN; j += 8) {
+    const int col = col0 + j;
+    if (col + 8 <= N && (reinterpret_cast<uintptr_t>(bias + col) & 15) == 0) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(bias + col));
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        r[j + 2 * q] = __float_as_uint(__uint_as_float(r[j + 2 * q]) + __uint_as_float(w[q] << 16));
+        r[j + 2 * q + 1] = __float_as_uint(__uint_as_float(r[j + 2 * q + 1]) + __uint_as_float(w[q] & 0xffff0000u));
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        if (col + q < N) r[j + q] = __float_as_uint(__uint_as_float(r[j + q]) + __bfloat162float(bias[col + q]));
+    }
+  }
+}
+
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t* r) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "

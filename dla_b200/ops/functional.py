@@ -65,12 +65,14 @@ def _slot_gemm(param: torch.Tensor) -> Tuple[Optional[torch.Tensor], bool]:
 # =======================================================================================
 
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
-         out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = BF16, accumulate: bool = False) -> torch.Tensor:
-    """``C[M,N] (+)= op(A) @ op(B)^T`` on the tcgen05 kernel.
+         out: Optional[torch.Tensor] = None, out_dtype: torch.dtype = BF16, accumulate: bool = False,
+         bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``C[M,N] (+)= op(A) @ op(B)^T (+ bias[N])`` on the tcgen05 kernel.
 
     ``a``: ``[M, K]`` (or ``[K, M]`` when ``a_mn``), ``b``: ``[N, K]`` (or ``[K, N]`` when ``b_mn``); both
     2-D with unit inner stride.  Shapes the TMA path cannot address (K or a pitch not a multiple
-    of 8, unaligned base) go to torch.matmul — a plain library GEMM, used only for odd shapes.
+    of 8, unaligned base) run the same kernel on zero-padded staging buffers (:func:`_gemm_padded`).
+    ``bias`` (bf16, K-major operands, no accumulate) is added to the fp32 accumulators in the GEMM epilogue.
     """
     assert a.dim() == 2 and b.dim() == 2
     M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
@@ -87,12 +89,21 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
           and b.stride(0) % 8 == 0 and a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0
           and out.stride(1) == 1 and out.dtype in (BF16, torch.float32)
           and (not a_mn or M % 8 == 0) and (not b_mn or Nn % 8 == 0))
+    if bias is not None:
+        assert not (a_mn or b_mn or accumulate) and bias.numel() == Nn, "gemm: bias goes with a plain forward product"
     if not ok:
         if a.is_cuda and a.dtype == BF16 and b.dtype == BF16 and out.dtype in (BF16, torch.float32):
-            return _gemm_padded(a, b, a_mn, b_mn, out, accumulate, M, Nn, K)
+            _gemm_padded(a, b, a_mn, b_mn, out, accumulate, M, Nn, K)
+            if bias is not None and out.dtype == BF16 and out.is_contiguous():
+                N.call("dla_add_bias", N.ptr(out), None, N.ptr(bias), N.ptr(out), M, Nn, _s(out))
+            elif bias is not None:
+                out.add_(bias.to(out.dtype))
+            return out
         am = a.t() if a_mn else a
         bm = b if b_mn else b.t()
         res = torch.matmul(am.to(torch.float32), bm.to(torch.float32))      # CPU tensors / non-bf16 dtypes only
+        if bias is not None:
+            res = res + bias.to(torch.float32)
         if accumulate:
             out.add_(res.to(out.dtype))
         else:
@@ -100,8 +111,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         return out
     if M <= SKINNY_MAX_ROWS and K % 32 == 0 and not (a_mn or b_mn or accumulate):
         # decode shapes: bound by the HBM stream of the weight, see csrc/skinny.cu
-        N.call("dla_gemm_skinny_bf16", N.ptr(a), N.ptr(b), N.ptr(out), None, None, M, Nn, K, a.stride(0), b.stride(0),
-               out.stride(0), 0, int(out.dtype == torch.float32), int(_STATIC_WEIGHTS[0]), _s(a))
+        N.call("dla_gemm_skinny_bf16", N.ptr(a), N.ptr(b), N.ptr(out), N.ptr(bias) if bias is not None else None, None, M, Nn, K,
+               a.stride(0), b.stride(0), out.stride(0), 0, int(out.dtype == torch.float32), int(_STATIC_WEIGHTS[0]), _s(a))
+        return out
+    if bias is not None:
+        N.call("dla_gemm_bias_bf16", N.ptr(a), N.ptr(b), N.ptr(out), N.ptr(bias), M, Nn, K, a.stride(0), b.stride(0), out.stride(0),
+               int(out.dtype == torch.float32), _s(a))
         return out
     N.call("dla_gemm_bf16", N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, a.stride(0), b.stride(0), out.stride(0),
            int(a_mn), int(b_mn), int(out.dtype == torch.float32), int(accumulate), _s(a))
@@ -183,10 +198,10 @@ class _Linear(Function):
         ag = getattr(w, "_ag", None)
         if ag is not None and not ag.done:
             y = ag.run(_c(x2))          # weight rows are all-gathered over NVLink inside this GEMM (path (b))
+            if bias is not None:
+                N.call("dla_add_bias", N.ptr(y), None, N.ptr(bias), N.ptr(y), y.shape[0], y.shape[1], _s(y))
         else:
-            y = gemm(x2, w)
-        if bias is not None:
-            N.call("dla_add_bias", N.ptr(y), None, N.ptr(bias), N.ptr(y), y.shape[0], y.shape[1], _s(y))
+            y = gemm(x2, w, bias=bias)      # the bias add rides in the GEMM epilogue
         ctx.save_for_backward(x2, w)
         ctx.has_bias = bias is not None
         ctx.bias_ref = bias

@@ -41,6 +41,7 @@ _SIGNATURES = {
     "dla_seq_mean_fwd": [P, P, P, I, I, I, P],
     "dla_seq_mean_bwd": [P, P, P, I, I, I, P],
     "dla_gemm_bf16": [P, P, P, I, I, I, I64, I64, I64, I, I, I, I, P],
+    "dla_gemm_bias_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I, P],
     "dla_gemm_set_variant": [I],
     "dla_gemm_swiglu_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],
     "dla_gemm_swiglu_bwd_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],

@@ -132,6 +132,12 @@ class Engine(ParamProvider):
         self.rs_in_backward = (self.fused and self.overlap_optimizer and _os.environ.get("DLA_RS_IN_BACKWARD", "1") != "0")
         self._rs_epoch = 0
         self._rs_launched: set = set()
+        # one GPU: a unit's share of the squared gradient norm is summed on the side stream as soon as its bucket is
+        # final, under the backward of the layers below it, instead of one 16 GB read after backward (DLA_NORM_IN_BACKWARD=0)
+        self.norm_in_backward = (self.ctx.world_size == 1 and self.device.type == "cuda" and self.overlap_optimizer
+                                 and _os.environ.get("DLA_NORM_IN_BACKWARD", "1") != "0")
+        self._sq_launched: set = set()
+        self._sq_stale = False
         self._train_ranges: Optional[Dict[str, List[tuple]]] = None     # set by freeze_except
         self.step_count = 0
         self._sumsq = None
@@ -459,6 +465,8 @@ class Engine(ParamProvider):
             return
         self._passes_seen[unit] = 0
         if self.ctx.world_size == 1:
+            if self.norm_in_backward and self.sync_grads:
+                self._launch_unit_sumsq(unit)
             return
         self._materialize_fresh(unit)
         if self.resident:
@@ -508,6 +516,27 @@ class Engine(ParamProvider):
                                 self.base[unit] + self.r * S, S, 1.0, self.gred[unit], self._sumsq)
         self.stats["reduce_bytes"] += S * _bytes(self.grad_dtype) * (1 if self.grad_arena.mc_ptr else self.W - 1)
         self._rs_launched.add(unit)
+
+    def _launch_unit_sumsq(self, unit: str) -> None:
+        """One GPU: this unit's bucket is final (everything enqueued so far on the current stream), so its sum of squares
+        can be read now, on the side stream, while the layers below still run their backward."""
+        if self._sumsq is None:
+            return
+        if unit in self._sq_launched:
+            self._sq_stale = True       # a second backward added to a bucket already summed: recompute at the step
+            return
+        self._materialize_fresh(unit)
+        self._zero_frozen(unit, local=True)
+        if self._opt_stream is None:
+            self._opt_stream = torch.cuda.Stream(device=self.device)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        self._opt_stream.wait_event(ev)
+        g = self._local_grad(unit)
+        with torch.cuda.stream(self._opt_stream):
+            N.call("dla_sumsq", N.ptr(g), g.numel(), int(g.dtype == torch.float32), N.ptr(self._sq_scratch),
+                   N.ptr(self._sumsq), 1, N.stream_ptr(self.device))
+        self._sq_launched.add(unit)
 
     def _drain(self, keep: int = 0) -> None:
         while len(self._reduce_work) > keep:
@@ -591,8 +620,19 @@ class Engine(ParamProvider):
                 self._zero_frozen(u.name, local=True)
         if cuda:
             s = N.stream_ptr(self.device)
-            self._sumsq.zero_()
+            if self._sq_launched and self._sq_stale:
+                torch.cuda.current_stream(self.device).wait_stream(self._opt_stream)
+                self._sq_launched.clear()
+            self._sq_stale = False
+            if self._sq_launched:
+                # partial sums of the units summed during backward are already in _sumsq (it was cleared after the last
+                # step's clip); the shared scratch is free once the side stream has drained
+                torch.cuda.current_stream(self.device).wait_stream(self._opt_stream)
+            else:
+                self._sumsq.zero_()
             for u in self.units:
+                if u.name in self._sq_launched:
+                    continue
                 g = self._local_grad(u.name)
                 N.call("dla_sumsq", N.ptr(g), g.numel(), int(g.dtype == torch.float32), N.ptr(self._sq_scratch),
                        N.ptr(self._sumsq), 1, s)
@@ -604,6 +644,9 @@ class Engine(ParamProvider):
                     dist.all_reduce(self._sumsq, group=self.ctx.group)
                 self._sumsq.mul_(prescale * prescale)
                 N.call("dla_clip_coef", N.ptr(self._sumsq), float(opt.max_grad_norm or 0.0), N.ptr(self._coef), N.ptr(self._norm), s)
+            if self.norm_in_backward:
+                self._sumsq.zero_()         # ready for the next backward's side-stream partial sums
+                self._sq_launched.clear()
             self._last_grad_norm = self._norm
         else:
             sq = torch.zeros((), dtype=torch.float64)

@@ -137,6 +137,11 @@ int dla_seq_mean_bwd(const float* dseq, const int64_t* mask, float* dtok, int B,
 int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
                   int64_t lda, int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major,
                   int c_fp32, int accumulate, void* stream);
+/* C[M,N] = A[M,K] * B[N,K]^T + bias[N] (bf16 bias, K-major operands): the bias add rides in the epilogue of either GEMM
+ * kernel on the fp32 accumulators, so a biased linear (GPT-2's c_attn / c_proj) is one launch and one rounding.
+ * R: nn.Linear(bias=True) / HF Conv1D under R/src/training/train_sft.py:66. */
+int dla_gemm_bias_bf16(const void* A, const void* B, void* C, const void* bias, int M, int N, int K,
+                       int64_t lda, int64_t ldb, int64_t ldc, int c_fp32, void* stream);
 /* Gate/up projection of a gated MLP with the activation in the GEMM epilogue (2-CTA kernel): B = [2F, K] holds the gate
  * rows then the up rows; ACT[M, F] = silu(A B_gate^T) * (A B_up^T), computed from the fp32 accumulators.  GU (nullable,
  * [M, 2F] bf16) additionally receives gate | up for a backward pass.  Needs F % 128 == 0, M >= 256 (DLA_E_UNSUPP

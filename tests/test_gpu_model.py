@@ -108,6 +108,56 @@ def test_engine_fast_paths_are_bit_identical_to_plain(native_lib, no_recompute):
         assert torch.equal(results[0][name], results[1][name]), f"unit {name} differs between plain and fast paths"
 
 
+def test_grad_norm_summed_during_backward_matches_the_pass_after_it(native_lib):
+    """One GPU: each unit's sum of squares is taken on the side stream as soon as the unit's backward is done.  Same
+    norm (to fp32 summation order) and same parameters as the single pass after backward; a second backward before the
+    optimizer step falls back to that pass."""
+    from dla_b200.models.factory import load_causal_lm
+    from dla_b200.optim import AdamWConfig
+    from dla_b200.parallel.pg import init_distributed
+
+    ctx = init_distributed()
+    ref = load_causal_lm("tiny-llama", ctx, gradient_checkpointing=False, trainable=False, seed=1, name="reference")
+    gen = torch.Generator().manual_seed(11)
+    batches = []
+    for i in range(4):
+        ids = (torch.randperm(ref.config.vocab_size - 4, generator=gen)[:4 * 96] + 4).view(4, 96).cuda()
+        ones = torch.ones_like(ids)
+        batches.append({"chosen": {"input_ids": ids[:2], "attention_mask": ones[:2]},
+                        "rejected": {"input_ids": ids[2:], "attention_mask": ones[2:]}})
+    out = []
+    for early in (False, True):
+        pol = load_causal_lm("tiny-llama", ctx, gradient_checkpointing=True, seed=2, name="policy")
+        eng = pol.engine
+        eng.norm_in_backward = early
+        eng.set_no_recompute_layers(1)
+        opt = AdamWConfig(lr=1e-3, weight_decay=0.01, max_grad_norm=0.05)       # small enough that the clip engages
+        norms = []
+        for step in range(3):
+            loss, _ = dpo_step(pol.model, ref.model, batches[step], beta=0.3)
+            loss.backward()
+            eng.finish_backward()
+            assert len(eng._sq_launched) == (len(eng.units) if early else 0)
+            eng.optimizer_step(opt)
+            norms.append(float(eng._last_grad_norm))
+        # two backwards into the same buckets, then one step: the early partial sums are stale and must not be used
+        for micro in range(2):
+            loss, _ = dpo_step(pol.model, ref.model, batches[3], beta=0.3)
+            loss.backward()
+            eng.finish_backward()
+        eng.optimizer_step(opt, grad_divisor=2.0)
+        norms.append(float(eng._last_grad_norm))
+        eng.sync_optimizer()
+        torch.cuda.synchronize()
+        out.append((norms, {u.name: eng.shard[u.name].float().clone() for u in eng.units}))
+    (n0, p0), (n1, p1) = out
+    assert all(n > 0.05 for n in n0), n0
+    for a, b in zip(n0, n1):
+        assert abs(a - b) <= 1e-5 * abs(a), (n0, n1)
+    for name in p0:
+        assert torch.allclose(p0[name], p1[name], rtol=1e-2, atol=1e-3), f"unit {name} differs"
+
+
 def test_packed_rows_equal_the_documents_run_one_by_one(native_lib):
     """``data.packing`` on the GPU: three documents packed into one row (segment ids + per-document positions) give
     each document the same token log-probs and the same weight gradients as running the documents as separate rows."""

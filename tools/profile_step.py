@@ -55,7 +55,9 @@ for ev in prof.events():
                 if key == "gemm_kernel":
                     key = "gemm_logprob" if "ELi1E" in name or ", 1>" in name or "(int)1>" in name else "gemm_store"
                 elif key == "gemm2_kernel":
-                    key = "gemm_2cta"
+                    fuse = 1 if ("ELi1E" in name or ", 1>" in name or "(int)1>" in name) else 2 if (
+                        "ELi2E" in name or ", 2>" in name or "(int)2>" in name) else 0
+                    key = ("gemm_2cta", "gemm_2cta+swiglu_fwd_epilogue", "gemm_2cta_dgrad+swiglu_bwd_epilogue")[fuse]
                 name = key
                 break
         if "at::native" in name:       # keep the functor name: which PyTorch elementwise ops are left in the step
@@ -95,4 +97,5 @@ for k, v in sorted(idle.items(), key=lambda kv: -kv[1][0])[:14]:
 fills.sort(reverse=True)
 print("largest fill / memset / memcpy events (us):", [(round(d, 1), n) for d, n in fills[:12]], "count", len(fills))
 Path(ROOT / "gpurun_out").mkdir(exist_ok=True)
-json.dump({"total_ms": total, "rows": rows[:40]}, open(ROOT / "gpurun_out" / "step_breakdown.json", "w"), indent=1)
+json.dump({"total_ms": total, "timeline_ms": (busy_until - t_first) / 1e3, "idle_ms": tot_idle / 1e3, "rows": rows[:40]},
+          open(ROOT / "gpurun_out" / "step_breakdown.json", "w"), indent=1)
