@@ -284,20 +284,28 @@ layernorm_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, co
 // ------------------------------------------------------------------------------- RoPE
 // grid: x over (head, 8-pair vector) of one token row, y over token rows (grid-stride): 32-bit index math only
 __global__ void __launch_bounds__(256)
-rope_kernel(bf16* __restrict__ x, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
-            const int32_t* __restrict__ positions, int64_t M, int n_heads, int head_dim, int rot_dim, int64_t row_stride,
-            float sign) {
+rope_kernel(const bf16* src, bf16* x, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
+            const int32_t* __restrict__ positions, int64_t M, int n_heads, int n_copy_heads, int head_dim, int rot_dim,
+            int64_t src_stride, int64_t row_stride, float sign) {
+  // src == x: in place.  Otherwise x receives the rotated q/k heads and a verbatim copy of the n_copy_heads heads that
+  // follow them (the v part of a packed projection), so the backward needs no clone of its incoming gradient.
   const int half = rot_dim >> 1;
   const int vec_per_head = half >> 3;  // 8 pairs per work item
   const int item = blockIdx.x * blockDim.x + threadIdx.x;
-  if (item >= n_heads * vec_per_head) return;
+  if (item >= (n_heads + n_copy_heads) * vec_per_head) return;
   const int h = item / vec_per_head, vi = item - h * vec_per_head;
   for (int64_t m = blockIdx.y; m < M; m += gridDim.y) {
-    const int pos = positions[m];
+    const bf16* in = src + m * src_stride + (int64_t)h * head_dim + vi * 8;
     bf16* base = x + m * row_stride + (int64_t)h * head_dim + vi * 8;
+    if (h >= n_heads) {
+      st8(base, ld8(in));
+      st8(base + half, ld8(in + half));
+      continue;
+    }
+    const int pos = positions[m];
     float a[8], b[8], c[8], s[8];
-    unpack8(ld8(base), a);
-    unpack8(ld8(base + half), b);
+    unpack8(ld8(in), a);
+    unpack8(ld8(in + half), b);
     const float4* cp = reinterpret_cast<const float4*>(cos_t + (int64_t)pos * half + vi * 8);
     const float4* sp = reinterpret_cast<const float4*>(sin_t + (int64_t)pos * half + vi * 8);
     *reinterpret_cast<float4*>(c) = cp[0];
@@ -593,9 +601,23 @@ int dla_rope_inplace(void* x, const float* cos_t, const float* sin_t, const int3
   const int items = n_heads * (rot_dim / 16);
   const int threads = items >= 256 ? 256 : ((items + 31) / 32) * 32;
   const dim3 grid((items + threads - 1) / threads, (unsigned)(M < 32768 ? M : 32768));
-  rope_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>((bf16*)x, cos_t, sin_t, positions, M, n_heads, head_dim, rot_dim,
-                                                          row_stride, sign);
+  rope_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>((const bf16*)x, (bf16*)x, cos_t, sin_t, positions, M, n_heads, 0, head_dim,
+                                                          rot_dim, row_stride, row_stride, sign);
   return check_launch("rope");
+}
+
+int dla_rope_copy(const void* src, void* dst, const float* cos_t, const float* sin_t, const int32_t* positions, int64_t M,
+                  int n_heads, int n_copy_heads, int head_dim, int64_t src_stride, int64_t dst_stride, float sign, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(head_dim % 16 == 0 && src_stride % 8 == 0 && dst_stride % 8 == 0 && src != dst, DLA_E_BADARG,
+              "rope_copy: head_dim=%d must be a multiple of 16, pitches multiples of 8, src != dst", head_dim);
+  if (M == 0 || n_heads + n_copy_heads == 0) return 0;
+  const int items = (n_heads + n_copy_heads) * (head_dim / 16);
+  const int threads = items >= 256 ? 256 : ((items + 31) / 32) * 32;
+  const dim3 grid((items + threads - 1) / threads, (unsigned)(M < 32768 ? M : 32768));
+  rope_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>((const bf16*)src, (bf16*)dst, cos_t, sin_t, positions, M, n_heads,
+                                                          n_copy_heads, head_dim, head_dim, src_stride, dst_stride, sign);
+  return check_launch("rope_copy");
 }
 
 int dla_swiglu_fwd(const void* gu, void* h, int64_t M, int F, void* stream) {

@@ -651,6 +651,8 @@ int gemm2_swiglu_dispatch(const void* A, const void* B, void* GU, void* ACT, int
                           int64_t ldgu, int64_t ldact, cudaStream_t stream);
 int gemm2_swiglu_bwd_dispatch(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H, int64_t lddy,
                               int64_t ldw, int64_t ldgu, int64_t lddgu, cudaStream_t stream);
+int gemm2_rope_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                        const float* cos_t, const float* sin_t, const int32_t* positions, int n_rot_heads, cudaStream_t stream);
 void gemm2_set_tail_split(int on);
 }
 
@@ -751,6 +753,18 @@ int dla_gemm_swiglu_bf16(const void* A, const void* B, void* GU, void* ACT, int 
   DLA_REQUIRE(((uintptr_t)ACT & 15) == 0 && (ldact * 2) % 16 == 0 && (GU == nullptr || ((((uintptr_t)GU & 15) == 0) && (ldgu * 2) % 16 == 0)),
               DLA_E_BADARG, "gemm_swiglu: outputs must be 16-byte aligned with 16-byte row pitch");
   return gemm2_swiglu_dispatch(A, B, GU, ACT, M, F, K, lda, ldb, ldgu, ldact, (cudaStream_t)stream);
+}
+
+int dla_gemm_rope_bf16(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                       const float* cos_t, const float* sin_t, const int32_t* positions, int n_rot_heads, void* stream) {
+  if (int rc_ = ::dla::ensure_device()) return rc_;
+  DLA_REQUIRE(M > 0 && N > 0 && K > 0 && K % 8 == 0, DLA_E_BADARG, "gemm_rope: bad shape %dx%dx%d", M, N, K);
+  DLA_REQUIRE(N % 128 == 0 && n_rot_heads >= 0 && n_rot_heads * 128 <= N, DLA_E_UNSUPP,
+              "gemm_rope: needs 128-wide heads (N=%d, n_rot_heads=%d)", N, n_rot_heads);
+  DLA_REQUIRE(cos_t != nullptr && sin_t != nullptr && positions != nullptr, DLA_E_BADARG, "gemm_rope: tables and positions are required");
+  DLA_REQUIRE(((uintptr_t)C & 15) == 0 && (ldc * 2) % 16 == 0 && (((uintptr_t)cos_t | (uintptr_t)sin_t) & 15) == 0, DLA_E_BADARG,
+              "gemm_rope: C and the tables must be 16-byte aligned, C with a 16-byte row pitch");
+  return gemm2_rope_dispatch(A, B, C, M, N, K, lda, ldb, ldc, cos_t, sin_t, positions, n_rot_heads, (cudaStream_t)stream);
 }
 
 int dla_gemm_swiglu_bwd_bf16(const void* dY, const void* Wdown, const void* GU, void* dGU, int M, int F, int H, int64_t lddy,

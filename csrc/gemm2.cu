@@ -14,6 +14,10 @@
 // separate SwiGLU pass (read 2F, write F per token) disappears; gate/up themselves are stored only when a backward
 // will need them.  Replaces K5 of SURVEY §2.6.2 as a stand-alone kernel on the forward path.
 //
+// kFuse == 3 (QKV projection of a Llama block, head_dim 128, full rotary): the 256-column tile is two heads; the epilogue
+// rotates (c, c + 64) column pairs of the q and k heads by the row's position on the fp32 accumulators and stores bf16
+// once, so RoPE is neither a separate pass over the packed projection nor a second rounding.
+//
 // kFuse == 2 (dgrad of the down projection): the epilogue turns its d(act) tile into d(gate) and d(up) on the spot — it
 // reads the saved gate / up values of the same rows and columns and stores both halves of d[gate | up]; d(act) itself
 // never reaches memory and the separate SwiGLU-backward pass disappears.
@@ -57,6 +61,11 @@ struct Params {
   const bf16* gu;   // kFuse 2: saved [M, 2F] gate | up
   int64_t ldgu;
   const bf16* bias; // kFuse 0: [N] added to every output row (forward linears with a bias; never with accumulate / tail split)
+  // kFuse 3: rotary embedding of the first n_rot_heads 128-wide heads of each output row (packed QKV projection)
+  const float* cos_t;          // [max_pos, 64]
+  const float* sin_t;
+  const int32_t* positions;    // [M]
+  int n_rot_heads;
 };
 
 // work item w -> (tile, K-block range).  Items below `full` are whole tiles; the rest are K slices of the tail tiles,
@@ -350,6 +359,60 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
           emit(d, c0);
           emit(o, p.F + c0);
         }
+      } else if constexpr (kFuse == 3) {
+        const int row = r0 + lane;
+        const int pos = row < p.M ? p.positions[row] : 0;
+        const float4* ct = reinterpret_cast<const float4*>(p.cos_t + (int64_t)pos * 64);
+        const float4* st = reinterpret_cast<const float4*>(p.sin_t + (int64_t)pos * 64);
+        uint8_t* lo_row = stage_base + lane * 128;              // columns [0, 64) of the head, this lane's row
+        uint8_t* hi_row = stage_base + 4096 + lane * 128;       // columns [64, 128)
+#pragma unroll 1
+        for (int hh = 0; hh < 2; ++hh) {
+          const int c0 = col_base + hh * 128;
+          if (c0 >= p.N) break;                     // (N % 128 == 0: a head is all in or all out)
+          const bool rot = (c0 >> 7) < p.n_rot_heads;
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous head's stores have read both buffers
+          __syncwarp();
+#pragma unroll 1
+          for (int q = 0; q < 2; ++q) {             // 32 rotation pairs at a time: (c, c + 64) for c in [32q, 32q + 32)
+            uint32_t lo[32], hi[32];
+            tc::tmem_ld_32x32(taddr + hh * 128 + q * 32, lo);
+            tc::tmem_ld_32x32(taddr + hh * 128 + 64 + q * 32, hi);
+            tc::tmem_ld_wait();
+            if (rot) {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const float4 c4 = __ldg(ct + q * 8 + j), s4 = __ldg(st + q * 8 + j);
+                const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float a = __uint_as_float(lo[4 * j + e]), b = __uint_as_float(hi[4 * j + e]);
+                  lo[4 * j + e] = __float_as_uint(a * cc[e] - b * ss[e]);
+                  hi[4 * j + e] = __float_as_uint(b * cc[e] + a * ss[e]);
+                }
+              }
+            }
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {           // 32 bf16 = four 16-byte chunks of the 128-byte staging row
+              const int chunk = ((q * 4 + c) ^ (lane & 7)) << 4;
+              *reinterpret_cast<uint4*>(lo_row + chunk) =
+                  make_uint4(pack2(lo[8 * c], lo[8 * c + 1]), pack2(lo[8 * c + 2], lo[8 * c + 3]), pack2(lo[8 * c + 4], lo[8 * c + 5]),
+                             pack2(lo[8 * c + 6], lo[8 * c + 7]));
+              *reinterpret_cast<uint4*>(hi_row + chunk) =
+                  make_uint4(pack2(hi[8 * c], hi[8 * c + 1]), pack2(hi[8 * c + 2], hi[8 * c + 3]), pack2(hi[8 * c + 4], hi[8 * c + 5]),
+                             pack2(hi[8 * c + 6], hi[8 * c + 7]));
+            }
+          }
+          tc::fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            if (r0 < p.M) {
+              tc::tma_store_2d(&tmC, stage_base, c0, r0);
+              tc::tma_store_2d(&tmC, stage_base + 4096, c0 + 64, r0);
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+        }
       } else
 #pragma unroll 1
       for (int gi = 0; gi < n_groups; ++gi) {
@@ -445,7 +508,7 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
   const int num_tiles = p.num_m_tiles * p.num_n_tiles;
   const int clusters = num_tiles < kNumSMs / 2 ? num_tiles : kNumSMs / 2;
   kern<<<2 * clusters, kThreads, SMEM_BYTES, stream>>>(tmA, tmB, tmC, tmD, p);
-  return check_launch(kFuse == 1 ? "gemm2_swiglu" : kFuse == 2 ? "gemm2_swiglu_bwd" : "gemm2_bf16");
+  return check_launch(kFuse == 1 ? "gemm2_swiglu" : kFuse == 2 ? "gemm2_swiglu_bwd" : kFuse == 3 ? "gemm2_rope" : "gemm2_bf16");
 }
 
 }  // namespace gemm2
@@ -497,6 +560,23 @@ int gemm2_dispatch(const void* A, const void* B, void* C, const void* bias, int 
   if (!a_mn && b_mn) return launch<false, true>(tmA, tmB, tmC, tmC, p, stream);
   if (a_mn && !b_mn) return launch<true, false>(tmA, tmB, tmC, tmC, p, stream);
   return launch<true, true>(tmA, tmB, tmC, tmC, p, stream);
+}
+
+// C[M, N] = rope(A[M,K] B[N,K]^T): the first n_rot_heads 128-wide heads of every row rotated by positions[row]
+int gemm2_rope_dispatch(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                        const float* cos_t, const float* sin_t, const int32_t* positions, int n_rot_heads, cudaStream_t stream) {
+  using namespace gemm2;
+  CUtensorMap tmA, tmB, tmC;
+  int rc;
+  if ((rc = make_tmap_2d_bf16(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM))) return rc;
+  if ((rc = make_tmap_2d_bf16(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, BNH))) return rc;
+  if ((rc = make_tmap_2d(&tmC, C, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (uint64_t)N, (uint64_t)M, (uint64_t)ldc, 64, 32))) return rc;
+  Params p{};
+  p.M = M; p.N = N; p.K = K; p.c_fp32 = 0; p.accumulate = 0;
+  p.num_m_tiles = (M + 255) / 256;
+  p.num_n_tiles = (N + BN - 1) / BN;
+  p.cos_t = cos_t; p.sin_t = sin_t; p.positions = positions; p.n_rot_heads = n_rot_heads;
+  return launch<false, false, 3>(tmA, tmB, tmC, tmC, p, stream);
 }
 
 // act[M, F] = silu(A W_gate^T) * (A W_up^T) with W = [gate rows | up rows] = B[2F, K]; gu (nullable) receives gate | up

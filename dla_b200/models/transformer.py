@@ -346,9 +346,9 @@ def _llama_layer(cfg: ModelConfig):
         # x: residual stream [B, T, H]; delta: the previous block's MLP output not yet added
         B, T, H = x.shape
         x, h = F.add_rmsnorm(x, delta, w["attn_norm"], cfg.norm_eps)
-        qkv = F.linear(h.reshape(B * T, H), w["wqkv"])
-        qkv = F.rope_qkv(qkv, positions.reshape(-1), Hq, Hk, D, cfg.rope_theta, cfg.rot_dim or None,
-                         max_pos=cfg.max_position_embeddings)
+        # RoPE rides in the QKV GEMM's epilogue where the shape allows (head_dim 128, full rotary), else a pass of its own
+        qkv = F.linear_rope_qkv(h.reshape(B * T, H), w["wqkv"], positions.reshape(-1), Hq, Hk, D, cfg.rope_theta,
+                                cfg.rot_dim or None, max_pos=cfg.max_position_embeddings)
         qkv4 = qkv.view(B, T, Hq + 2 * Hk, D)
         attn = F.attention_qkv(qkv4, Hq, Hk, seqlens=seqlens, causal=True, segment_ids=segment_ids)
         a = F.linear(attn.reshape(B, T, Hq * D), w["wo"])

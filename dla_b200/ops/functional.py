@@ -375,6 +375,13 @@ class _RopeQKV(Function):
     def backward(ctx, g):
         positions, cos, sin = ctx.saved_tensors
         n_rot_heads, head_dim, rot_dim = ctx.meta
+        width = g.shape[1]
+        if rot_dim == head_dim and head_dim % 16 == 0 and width % head_dim == 0 and g.stride(1) == 1 and g.stride(0) % 8 == 0:
+            # the incoming gradient must not be modified: rotate q/k and copy v into a fresh tensor in ONE pass
+            out = torch.empty(g.shape, dtype=g.dtype, device=g.device)
+            N.call("dla_rope_copy", N.ptr(g), N.ptr(out), N.ptr(cos), N.ptr(sin), N.ptr(positions), g.shape[0], n_rot_heads,
+                   width // head_dim - n_rot_heads, head_dim, g.stride(0), out.stride(0), -1.0, _s(g))
+            return out, None, None, None, None, None, None
         g = g.clone(memory_format=torch.contiguous_format)
         N.call("dla_rope_inplace", N.ptr(g), N.ptr(cos), N.ptr(sin), N.ptr(positions), g.shape[0], n_rot_heads,
                head_dim, rot_dim, g.stride(0), -1.0, _s(g))
@@ -394,6 +401,61 @@ def rope_qkv(qkv: torch.Tensor, positions: torch.Tensor, n_q: int, n_kv: int, he
     cos, sin = rope_tables(max_pos, rd, theta, qkv.device)
     pos32 = positions.to(torch.int32)
     return _RopeQKV.apply(qkv, pos32, cos, sin, n_q + n_kv, head_dim, rd)
+
+
+FUSE_ROPE = _os.environ.get("DLA_FUSE_ROPE", "1") != "0"
+
+
+class _LinearRopeQKV(Function):
+    """Packed QKV projection with RoPE in the GEMM epilogue (``dla_gemm_rope_bf16``): the q and k heads are rotated on
+    the fp32 accumulators and rounded once.  Backward: inverse rotation of the incoming gradient (one out-of-place
+    pass), then the usual dgrad / wgrad GEMMs with the gradient-slot protocol of :class:`_Linear`."""
+
+    @staticmethod
+    def forward(ctx, x2, w, positions, cos, sin, n_rot_heads, head_dim):
+        M, K = x2.shape
+        Nn = w.shape[0]
+        y = torch.empty(M, Nn, dtype=BF16, device=x2.device)
+        N.call("dla_gemm_rope_bf16", N.ptr(x2), N.ptr(w), N.ptr(y), M, Nn, K, x2.stride(0), w.stride(0), y.stride(0),
+               N.ptr(cos), N.ptr(sin), N.ptr(positions), n_rot_heads, _s(x2))
+        ctx.save_for_backward(x2, w, positions, cos, sin)
+        ctx.wref = w
+        ctx.meta = (n_rot_heads, head_dim)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, positions, cos, sin = ctx.saved_tensors
+        n_rot_heads, head_dim = ctx.meta
+        dy = dy if (dy.stride(1) == 1 and dy.stride(0) % 8 == 0) else dy.contiguous()
+        g = torch.empty(dy.shape, dtype=dy.dtype, device=dy.device)
+        N.call("dla_rope_copy", N.ptr(dy), N.ptr(g), N.ptr(cos), N.ptr(sin), N.ptr(positions), dy.shape[0], n_rot_heads,
+               dy.shape[1] // head_dim - n_rot_heads, head_dim, dy.stride(0), g.stride(0), -1.0, _s(dy))
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(g, w, b_mn=True)
+        if ctx.needs_input_grad[1]:
+            slot, acc = _slot_gemm(ctx.wref)
+            if slot is not None:
+                gemm(g, x2, a_mn=True, b_mn=True, out=slot, accumulate=acc)
+            else:
+                dw = gemm(g, x2, a_mn=True, b_mn=True)
+        return dx, dw, None, None, None, None, None
+
+
+def linear_rope_qkv(x2: torch.Tensor, w: torch.Tensor, positions: torch.Tensor, n_q: int, n_kv: int, head_dim: int,
+                    theta: float, rot_dim: Optional[int] = None, max_pos: int = 8192) -> torch.Tensor:
+    """``rope_qkv(linear(x2, w))`` for a packed ``[(n_q + 2 n_kv) * D, K]`` projection weight, as ONE kernel when the
+    shape allows it (CUDA, head_dim 128, full rotary, enough rows for the 2-CTA kernel, weight resident)."""
+    rd = rot_dim or head_dim
+    fused = (FUSE_ROPE and x2.is_cuda and x2.dim() == 2 and head_dim == 128 and rd == 128 and x2.shape[0] >= 256
+             and x2.dtype == BF16 and w.dtype == BF16 and x2.shape[1] % 8 == 0 and x2.stride(1) == 1 and w.stride(1) == 1
+             and x2.stride(0) % 8 == 0 and w.stride(0) % 8 == 0 and x2.data_ptr() % 16 == 0 and w.data_ptr() % 16 == 0
+             and w.shape[0] == (n_q + 2 * n_kv) * head_dim and getattr(w, "_ag", None) is None)
+    if not fused:
+        return rope_qkv(linear(x2, w), positions, n_q, n_kv, head_dim, theta, rot_dim, max_pos=max_pos)
+    cos, sin = rope_tables(max_pos, rd, theta, x2.device)
+    return _LinearRopeQKV.apply(x2, w, positions.to(torch.int32), cos, sin, n_q + n_kv, head_dim)
 
 
 # =======================================================================================

@@ -24,6 +24,7 @@ _SIGNATURES = {
     "dla_layernorm_fwd": [P, P, P, P, P, I64, I, F, P],
     "dla_layernorm_bwd": [P, P, P, P, P, P, P, P, I, I64, I, P],
     "dla_rope_inplace": [P, P, P, P, I64, I, I, I, I64, F, P],
+    "dla_rope_copy": [P, P, P, P, P, I64, I, I, I, I64, I64, F, P],
     "dla_swiglu_fwd": [P, P, I64, I, P],
     "dla_swiglu_bwd": [P, P, P, I64, I, P],
     "dla_gelu_fwd": [P, P, P, I64, I, P],
@@ -42,6 +43,7 @@ _SIGNATURES = {
     "dla_seq_mean_bwd": [P, P, P, I, I, I, P],
     "dla_gemm_bf16": [P, P, P, I, I, I, I64, I64, I64, I, I, I, I, P],
     "dla_gemm_bias_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I, P],
+    "dla_gemm_rope_bf16": [P, P, P, I, I, I, I64, I64, I64, P, P, P, I, P],
     "dla_gemm_set_variant": [I],
     "dla_gemm_swiglu_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],
     "dla_gemm_swiglu_bwd_bf16": [P, P, P, P, I, I, I, I64, I64, I64, I64, P],

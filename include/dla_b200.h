@@ -63,6 +63,12 @@ int dla_layernorm_bwd(const void* dy, const void* x, const void* w, const float*
 int dla_rope_inplace(void* x, const float* cos_t, const float* sin_t, const int32_t* positions,
                      int64_t M, int n_heads, int head_dim, int rot_dim, int64_t row_stride,
                      float sign, void* stream);
+/* Out-of-place form (full rotary, rot_dim == head_dim): dst receives the rotated first n_heads heads of src and a verbatim
+ * copy of the n_copy_heads heads after them (the v part).  The backward uses it on its incoming gradient, which it may
+ * not modify: one read + one write instead of a clone followed by the in-place pass. */
+int dla_rope_copy(const void* src, void* dst, const float* cos_t, const float* sin_t, const int32_t* positions,
+                  int64_t M, int n_heads, int n_copy_heads, int head_dim, int64_t src_stride,
+                  int64_t dst_stride, float sign, void* stream);
 
 /* ---------------------------------------------------------------- activations (K5) */
 /* h = silu(gu[:, :F]) * gu[:, F:] ; gu bf16 [M, 2F], h bf16 [M, F]. */
@@ -142,6 +148,13 @@ int dla_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K,
  * R: nn.Linear(bias=True) / HF Conv1D under R/src/training/train_sft.py:66. */
 int dla_gemm_bias_bf16(const void* A, const void* B, void* C, const void* bias, int M, int N, int K,
                        int64_t lda, int64_t ldb, int64_t ldc, int c_fp32, void* stream);
+/* QKV projection with RoPE in the epilogue (2-CTA kernel, head_dim 128, full rotary): C[M,N] = A[M,K] B[N,K]^T with the
+ * first n_rot_heads 128-wide heads of every row rotated (rotate-half pairs (c, c+64)) by positions[row] on the fp32
+ * accumulators; cos/sin fp32 [max_pos, 64], positions int32 [M].  N % 128 == 0 (DLA_E_UNSUPP otherwise: run
+ * dla_gemm_bf16 + dla_rope_inplace).  R: HF LlamaAttention q_proj/k_proj + apply_rotary_pos_emb under
+ * R/src/training/train_dpo.py:32 (K1 + K4). */
+int dla_gemm_rope_bf16(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda, int64_t ldb, int64_t ldc,
+                       const float* cos_t, const float* sin_t, const int32_t* positions, int n_rot_heads, void* stream);
 /* Gate/up projection of a gated MLP with the activation in the GEMM epilogue (2-CTA kernel): B = [2F, K] holds the gate
  * rows then the up rows; ACT[M, F] = silu(A B_gate^T) * (A B_up^T), computed from the fp32 accumulators.  GU (nullable,
  * [M, 2F] bf16) additionally receives gate | up for a backward pass.  Needs F % 128 == 0, M >= 256 (DLA_E_UNSUPP

@@ -81,7 +81,9 @@ def test_rope_qkv(native_lib):
     _close(out, want, what="rope fwd")
     # rotation is orthogonal: backward of sum(out * g) is the inverse rotation of g
     g = _rand(M, (Hq + 2 * Hk) * D)
+    g_before = g.clone()
     out.backward(g)
+    assert torch.equal(g, g_before), "the backward must not modify its incoming gradient"
     gq, gk, gv = g.float().split([Hq * D, Hk * D, Hk * D], -1)
     xq = qkv.float().requires_grad_()
     q2, k2, v2 = xq.split([Hq * D, Hk * D, Hk * D], -1)
@@ -774,3 +776,45 @@ def test_linear_with_bias_is_one_launch(native_lib):
         y = F.linear(x, w, b)
         assert Nat.launch_count() - n0 == 1
     _close(y, torch.nn.functional.linear(x.float(), w.float(), b.float()), what="linear+bias")
+
+
+@pytest.mark.parametrize("B,T,Hq,Hk,K", [(2, 128, 4, 2, 512), (3, 200, 8, 2, 1024), (8, 1024, 32, 8, 4096)])
+def test_qkv_projection_with_rope_epilogue(native_lib, B, T, Hq, Hk, K):
+    """RoPE in the QKV GEMM's epilogue (2-CTA kernel, fp32 accumulators rotated, one rounding) vs the fp32 reference and
+    vs the two-kernel path; backward through the out-of-place inverse rotation."""
+    torch.manual_seed(B * T + K)
+    D, M = 128, B * T
+    x, w = _rand(M, K, scale=0.5), _rand((Hq + 2 * Hk) * D, K, scale=0.05)
+    pos = (torch.arange(T, device=DEV).repeat(B) + 3) % 777                  # not just 0..T-1
+    g = _rand(M, (Hq + 2 * Hk) * D)
+
+    def ref(xf, wf):
+        y = xf @ wf.t()
+        q, k, v = y.split([Hq * D, Hk * D, Hk * D], -1)
+        qr = R.rope(q.reshape(1, M, Hq, D), pos.reshape(1, M), 500000.0).reshape(M, -1)
+        kr = R.rope(k.reshape(1, M, Hk, D), pos.reshape(1, M), 500000.0).reshape(M, -1)
+        return torch.cat([qr, kr, v], -1)
+
+    xr, wr = x.float().requires_grad_(), w.float().requires_grad_()
+    want = ref(xr, wr)
+    (want * g.float()).sum().backward()
+    outs = {}
+    for fused in (True, False):
+        F.FUSE_ROPE = fused
+        try:
+            xa, wa = x.clone().requires_grad_(), w.clone().requires_grad_()
+            y = F.linear_rope_qkv(xa, wa, pos, Hq, Hk, D, 500000.0, max_pos=1024)
+            y.backward(g)
+        finally:
+            F.FUSE_ROPE = True
+        outs[fused] = (y.detach(), xa.grad, wa.grad)
+        _rel(y, want, 6e-3, what=f"qkv+rope fwd fused={fused}")
+        _rel(xa.grad, xr.grad, 8e-3, what=f"dx fused={fused}")
+        _rel(wa.grad, wr.grad, 8e-3, what=f"dw fused={fused}")
+    # one rounding instead of two: the fused output is at least as close to fp32 as the two-kernel one
+    e_f = (outs[True][0].float() - want).norm().item()
+    e_u = (outs[False][0].float() - want).norm().item()
+    assert e_f <= e_u * 1.02, (e_f, e_u)
+    # same backward math on both paths (small-M dgrads meet their K slices by bf16 reduce-add, so not bit-for-bit)
+    _rel(outs[True][1], outs[False][1], 4e-3, what="dx fused vs two-kernel")
+    _rel(outs[True][2], outs[False][2], 4e-3, what="dw fused vs two-kernel")
