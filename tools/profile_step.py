@@ -55,9 +55,12 @@ for ev in prof.events():
                 if key == "gemm_kernel":
                     key = "gemm_logprob" if "ELi1E" in name or ", 1>" in name or "(int)1>" in name else "gemm_store"
                 elif key == "gemm2_kernel":
-                    fuse = 1 if ("ELi1E" in name or ", 1>" in name or "(int)1>" in name) else 2 if (
-                        "ELi2E" in name or ", 2>" in name or "(int)2>" in name) else 0
-                    key = ("gemm_2cta", "gemm_2cta+swiglu_fwd_epilogue", "gemm_2cta_dgrad+swiglu_bwd_epilogue")[fuse]
+                    fuse = 0
+                    for f in (1, 2, 3):
+                        if f"ELi{f}E" in name or f", {f}>" in name or f"(int){f}>" in name:
+                            fuse = f
+                    key = ("gemm_2cta", "gemm_2cta+swiglu_fwd_epilogue", "gemm_2cta_dgrad+swiglu_bwd_epilogue",
+                           "gemm_2cta_qkv+rope_epilogue")[fuse]
                 name = key
                 break
         if "at::native" in name:       # keep the functor name: which PyTorch elementwise ops are left in the step
