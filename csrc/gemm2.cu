@@ -295,7 +295,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
           for (int c = 0; c < 64; ++c) {
             const float gv = __uint_as_float(g[c]);
-            g[c] = __float_as_uint(gv / (1.f + __expf(-gv)) * __uint_as_float(u[c]));
+            g[c] = __float_as_uint(gv * __fdividef(1.f, 1.f + __expf(-gv)) * __uint_as_float(u[c]));   // fast reciprocal: the result is rounded to bf16
           }
           emit(&tmD, g, fc0);
         }
@@ -350,7 +350,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
               const float da = __uint_as_float(d[c * 8 + e]);
-              const float sg = 1.f / (1.f + __expf(-g8[e]));
+              const float sg = __fdividef(1.f, 1.f + __expf(-g8[e]));
               const float silu = g8[e] * sg;
               o[c * 8 + e] = __float_as_uint(da * silu);                                       // d(up)
               d[c * 8 + e] = __float_as_uint(da * u8[e] * sg * (1.f + g8[e] * (1.f - sg)));   // d(gate)

@@ -77,5 +77,32 @@ elif what == "adamw":
     for _ in range(3):
         N.call("dla_adamw", N.ptr(master), N.ptr(m), N.ptr(v), N.ptr(g), N.ptr(prm), n, 1e-5, 0.9, 0.999, 1e-8, 0.01, 0.1, 0.001,
                N.ptr(coef), 1.0, 0, N.stream_ptr())
+elif what == "mlp_epilogues":      # gate/up GEMM with the SwiGLU epilogue (kFuse 1) and the down dgrad with its backward (kFuse 2)
+    h = r(8192, 4096).requires_grad_()
+    w_gu, w_down = (r(28672, 4096) * 0.02).requires_grad_(), (r(4096, 14336) * 0.02).requires_grad_()
+    for _ in range(2):
+        y = F.mlp_swiglu(h, w_gu, w_down)
+        torch.autograd.grad(y, [h, w_gu, w_down], torch.ones_like(y))
+elif what == "qkv_rope":           # QKV GEMM with the RoPE epilogue (kFuse 3)
+    h, w = r(8192, 4096), r(6144, 4096) * 0.02
+    pos = torch.arange(1024, device=dev).repeat(8)
+    for _ in range(3):
+        F.linear_rope_qkv(h, w, pos, 32, 8, 128, 500000.0, None, max_pos=8192)
+elif what == "ag_gemm":            # all-gather fused GEMM with this GPU as the only "peer": copy CTAs + flag-gated tiles, no NVLink
+    from dla_b200.ops import native as N
+    M, Nn, K = 8192, 6144, 4096
+    a = r(M, K)
+    shard = r(Nn * K) * 0.02            # the "unit": one weight matrix, world = 1
+    full = torch.empty_like(shard)
+    c = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
+    flags = torch.zeros(8192, dtype=torch.int32, device=dev)
+    dptrs = torch.tensor([shard.data_ptr()], dtype=torch.int64, device=dev)
+    for ep in range(1, 4):
+        N.call("dla_ag_gemm_bf16", N.ptr(a), N.ptr(dptrs), N.ptr(full), Nn * K, 0, N.ptr(c), M, Nn, K, K, Nn, 1, 0, N.ptr(flags), ep, 8, 0,
+               N.stream_ptr())
+    torch.cuda.synchronize()
+    ref = a.float() @ shard.view(Nn, K).float().t()
+    err = ((c.float() - ref).norm() / ref.norm()).item()
+    assert err < 1e-2, err
 torch.cuda.synchronize()
 print("ok", what)
