@@ -199,8 +199,12 @@ def _e2e_stream_worker(rank, world, port, out):
     from dla_b200.config import HardwarePlan
     from dla_b200.data.synthetic import synthetic_preference_batch
     from dla_b200.models.factory import load_causal_lm
+    from dla_b200.ops import functional as F
     from dla_b200.optim import AdamWConfig
 
+    # this test compares two ways of moving the same bytes: keep the math identical (the all-gather GEMM has no RoPE
+    # epilogue, so its arm rounds the projection before rotating it; the NCCL arm would rotate the fp32 accumulators)
+    F.FUSE_ROPE = False
     res = {}
     for comm in ("nccl", "fused"):
         plan = HardwarePlan(sharding="zero3", comm=comm, resident_params=False)
