@@ -855,6 +855,8 @@ class Engine(ParamProvider):
     def zero_grad(self) -> None:
         if torch.cuda.is_available() and self.device.type == "cuda" and torch.cuda.current_stream(self.device) != self._opt_stream:
             self.sync_optimizer()
+        if self._sq_launched:
+            self._sq_stale = True       # partial norms taken during a backward whose gradients are now discarded
         for k in self.gradbuf:
             self._zero_unit(k)
         for g in self.gshard.values():

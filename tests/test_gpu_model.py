@@ -147,6 +147,16 @@ def test_grad_norm_summed_during_backward_matches_the_pass_after_it(native_lib):
             eng.finish_backward()
         eng.optimizer_step(opt, grad_divisor=2.0)
         norms.append(float(eng._last_grad_norm))
+        # a backward whose gradients are thrown away must not leave its partial sums behind
+        loss, _ = dpo_step(pol.model, ref.model, batches[0], beta=0.3)
+        loss.backward()
+        eng.finish_backward()
+        eng.zero_grad()
+        loss, _ = dpo_step(pol.model, ref.model, batches[1], beta=0.3)
+        loss.backward()
+        eng.finish_backward()
+        eng.optimizer_step(opt)
+        norms.append(float(eng._last_grad_norm))
         eng.sync_optimizer()
         torch.cuda.synchronize()
         out.append((norms, {u.name: eng.shard[u.name].float().clone() for u in eng.units}))
