@@ -189,7 +189,24 @@ class OwnArm:
                 "activation_checkpointing": f"per layer; last {len(self.eng.no_recompute)} of {self.policy.config.num_layers} "
                                             f"layers keep activations (free HBM)",
                 "comm": ("fused peer-memory" if getattr(self.eng, "fused", False) or getattr(self.eng, "fused_ddp", False)
-                         or getattr(self.eng, "fused_stream", False) else ("nccl" if self.world > 1 else "none"))}
+                         or getattr(self.eng, "fused_stream", False) else ("nccl" if self.world > 1 else "none")),
+                "comm_detail": self._comm_detail()}
+
+    def _comm_detail(self) -> dict:
+        """What moved the gradients / parameters between GPUs (the engine's own byte counters over the whole run: a claim
+        like ``gpu_launches``, here so the record says more than "N ranks")."""
+        try:
+            eng = self.eng
+            fused = bool(getattr(eng, "fused", False) or getattr(eng, "fused_ddp", False) or getattr(eng, "fused_stream", False))
+            arena = getattr(eng, "grad_arena", None)
+            return {"gradient_exchange": ("per-unit reduce-scatter kernel inside backward (dla_unit_reduce)" if getattr(eng, "rs_in_backward", False)
+                                          else "fused kernels after backward" if fused else "nccl" if self.world > 1 else "none"),
+                    "nvswitch_multicast": bool(getattr(arena, "mc_ptr", 0)) if fused else False,
+                    "optimizer_steps": int(eng.step_count),
+                    "reduce_bytes_per_rank_total": int(eng.stats.get("reduce_bytes", 0)),
+                    "param_publish_bytes_per_rank_total": int(eng.stats.get("allgather_bytes", 0))}
+        except Exception as e:       # never let a diagnostic break the record
+            return {"error": f"{type(e).__name__}: {e}"[:120]}
 
 
 def main() -> None:

@@ -409,3 +409,23 @@ def test_non_finite_gradient_norm_skips_the_whole_update():
         a, b, c = snap[u.name]
         assert torch.equal(a, eng.master[u.name]) and torch.equal(b, eng.m[u.name]) and torch.equal(c, eng.v[u.name])
         assert torch.isfinite(eng.shard[u.name]).all()
+
+
+def test_bench_comm_detail_never_raises_and_names_the_exchange():
+    """The bench record's ``comm_detail`` is a diagnostic: it must describe each engine mode and can never break the line."""
+    import importlib.util
+    from types import SimpleNamespace as NS
+
+    spec = importlib.util.spec_from_file_location("bench_mod", ROOT / "bench.py")
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    detail = bench.OwnArm._comm_detail
+    eng = NS(fused=True, rs_in_backward=True, grad_arena=NS(mc_ptr=1234), step_count=8, stats={"reduce_bytes": 10, "allgather_bytes": 20})
+    d = detail(NS(eng=eng, world=8))
+    assert "inside backward" in d["gradient_exchange"] and d["nvswitch_multicast"] is True
+    assert d["optimizer_steps"] == 8 and d["reduce_bytes_per_rank_total"] == 10 and d["param_publish_bytes_per_rank_total"] == 20
+    d = detail(NS(eng=NS(step_count=3, stats={}), world=1))
+    assert d["gradient_exchange"] == "none" and d["nvswitch_multicast"] is False
+    d = detail(NS(eng=NS(step_count=3, stats={}), world=4))
+    assert d["gradient_exchange"] == "nccl"
+    assert "error" in detail(NS(eng=None, world=2))
