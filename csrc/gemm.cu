@@ -534,9 +534,20 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             }
           }
           if ((rel >> 5) == ch && rel >= 0) {
+            // r[rel & 31] by a 5-level select tree on the index bits: static register indices only.  (The obvious compare
+            // chain was compiled into a dynamically indexed read of a local-memory copy of r, i.e. 128 bytes of local
+            // stores per lane and chunk for every row, taken or not.)
+            const int jj = rel & 31;
+            uint32_t s16[16], s8[8], s4[4], s2[2];
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j == (rel & 31)) picked = __uint_as_float(r[j]);
+            for (int k = 0; k < 16; ++k) s16[k] = (jj & 16) ? r[k + 16] : r[k];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) s8[k] = (jj & 8) ? s16[k + 8] : s16[k];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) s4[k] = (jj & 4) ? s8[k + 4] : s8[k];
+#pragma unroll
+            for (int k = 0; k < 2; ++k) s2[k] = (jj & 2) ? s4[k + 2] : s4[k];
+            picked = __uint_as_float((jj & 1) ? s2[1] : s2[0]);
             has_pick = true;
           }
         }
