@@ -99,7 +99,10 @@ def main() -> None:
     rng = random.Random(seed)
 
     while not loop.done():
-        batch_prompts = rng.sample(prompts, k=min(batch_size, len(prompts)))           # identical on all ranks
+        k = min(batch_size, len(prompts))
+        if ctx.world_size > 1 and k >= ctx.world_size:
+            k -= k % ctx.world_size        # equal shares per rank: the cross-rank gathers (fused kernel or NCCL) carry ONE row count
+        batch_prompts = rng.sample(prompts, k=k)                                        # identical on all ranks
         local_prompts = split_between_processes(batch_prompts, ctx.world_size, ctx.rank)
         if not local_prompts:
             local_prompts = batch_prompts[:1]
@@ -135,10 +138,12 @@ def main() -> None:
                     return loss
                 with torch.no_grad():
                     rewards_local = scores - kl_coef * (pol.detach() - refl)
-                    baseline = ctx.gather(rewards_local).mean()                      # global baseline
+                    n_local = torch.tensor(float(rewards_local.numel()), device=rewards_local.device)
+                    tot = ctx.all_reduce(torch.stack([rewards_local.sum().float(), n_local]), "sum")
+                    baseline = tot[0] / tot[1]                                       # global baseline, any row counts
                 loss, kl, rewards = reinforce_step(pol, refl, scores, kl_coef, baseline)
-                glob = ctx.all_reduce(torch.stack([kl.detach().mean(), rewards.detach().mean(), scores.mean()]).float(), "mean")
-                info.update(kl=glob[0], reward=glob[1], score=glob[2])
+                glob = ctx.all_reduce(torch.stack([kl.detach().sum(), rewards.detach().sum(), scores.sum(), n_local]).float(), "sum")
+                info.update(kl=glob[0] / glob[3], reward=glob[1] / glob[3], score=glob[2] / glob[3])
                 return loss
             loss = loop.micro_step(loss_fn)
         else:

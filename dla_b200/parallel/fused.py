@@ -223,7 +223,9 @@ class FusedComm:
 
 
     def reinforce_loss(self, pol: torch.Tensor, ref: torch.Tensor, score: torch.Tensor, kl_coef: float):
-        """Returns (out [loss, mean kl, mean reward, mean score, baseline] over the GLOBAL batch, dpol [B])."""
+        """Returns (out [loss, mean kl, mean reward, mean score, baseline] over the GLOBAL batch, dpol [B]).
+        Every rank must pass the same number of rows (the kernel reads ``world x B`` entries; ``cli.train_rlhf`` trims
+        the global batch to a multiple of the world size for that reason)."""
         B = pol.numel()
         assert B <= DPO_BMAX
         out = torch.empty(5, dtype=torch.float32, device=pol.device)

@@ -337,3 +337,35 @@ def test_reference_arm_param_count_formula():
 
     assert abs(ra.param_bytes(ra.llama_hf_config("llama3-8b")) / 2 - 8.03e9) < 0.01e9
     assert abs(ra.param_bytes(ra.llama_hf_config("llama3-70b")) / 2 - 70.55e9) < 0.05e9
+
+
+@pytest.mark.timeout(900)
+def test_clipped_ppo_gloo_world2_uneven_batches_and_global_early_stop(tmp_path):
+    """Clipped PPO (value head, GAE, mini-batches) and REINFORCE on 2 gloo ranks with a batch size that does not split
+    evenly (5 prompts; the loop trims the global batch to equal shares, since the cross-rank gathers carry one row count)
+    and a ``target_kl`` so small that the early stop fires: the stop decision and the number of mini-batches must be the
+    same on both ranks, or the next collective hangs.  The job has to finish, for both algorithms."""
+    import yaml
+
+    prompts = tmp_path / "prompts.jsonl"
+    prompts.write_text("\n".join(json.dumps({"prompt": f"Tell me about {i}"}) for i in range(10)) + "\n")
+    base = {"seed": 5, "model": {"policy_model_name_or_path": "tiny-llama", "reference_model_name_or_path": "tiny-llama", "max_seq_length": 32},
+            "reward_model": {"base_model_name_or_path": "tiny-llama"},
+            "ppo": {"steps": 2, "batch_size": 5, "learning_rate": 1e-4, "kl_coef": 0.1,
+                    "generation_params": {"max_new_tokens": 4, "temperature": 0.7, "top_p": 0.9, "do_sample": True}},
+            "sampling": {"source": "local", "prompt_path": str(prompts)},
+            "hardware": {"device": "cpu"}}
+    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="")
+    for algo, extra in (("ppo", {"algo": "ppo", "mini_batch_size": 2, "epochs": 2, "target_kl": 1e-12}), ("reinforce", {})):
+        cfg = json.loads(json.dumps(base))
+        cfg["ppo"].update(extra)
+        cfg["logging"] = {"output_dir": str(tmp_path / algo / "ck"), "log_dir": str(tmp_path / algo / "logs"), "log_every_steps": 1}
+        path = tmp_path / f"rlhf_{algo}.yaml"
+        path.write_text(yaml.safe_dump(cfg))
+        cmd = [sys.executable, "-m", "dla_b200.cli.launch", "--cpu", "--nproc", "2", "--port", str(_free_port()), "-m",
+               "dla_b200.cli.train_rlhf", "--config", str(path)]
+        res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=400)
+        assert res.returncode == 0, f"{algo}:\n" + res.stdout[-2500:] + res.stderr[-2500:]
+        assert "RLHF PPO loop complete" in res.stdout
+        lines = [json.loads(l) for l in (tmp_path / algo / "logs" / "metrics.jsonl").read_text().splitlines()]
+        assert any("train/kl" in l for l in lines)
