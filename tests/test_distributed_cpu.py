@@ -369,3 +369,53 @@ def test_clipped_ppo_gloo_world2_uneven_batches_and_global_early_stop(tmp_path):
         assert "RLHF PPO loop complete" in res.stdout
         lines = [json.loads(l) for l in (tmp_path / algo / "logs" / "metrics.jsonl").read_text().splitlines()]
         assert any("train/kl" in l for l in lines)
+
+
+@pytest.mark.timeout(900)
+def test_sft_reward_distill_cli_gloo_world2(tmp_path):
+    """The other trainers on 2 gloo ranks (ZeRO-3), with their evaluation loops (cross-rank loss gathers) and checkpoints:
+    SFT -> reward model from the SFT checkpoint -> distillation (ensemble KL) from it."""
+    import yaml
+
+    sft = [{"prompt": f"Question {i}: what is {i}+{i}?", "response": f"It is {2 * i}."} for i in range(22)]      # 22: not a multiple of 4
+    pref = [{"prompt": f"Say {i}", "chosen": f"{i} indeed", "rejected": "no"} for i in range(22)]
+    roll = [{"prompt": f"Tell me about {i}", "teacher_response": f"{i} is a number.", "reward": 0.1 * i} for i in range(10)]
+    for name, rows in (("sft.jsonl", sft), ("pref.jsonl", pref), ("roll.jsonl", roll)):
+        (tmp_path / name).write_text("\n".join(json.dumps(r) for r in rows) + "\n")
+    env = dict(os.environ, PYTHONPATH=str(ROOT), OMP_NUM_THREADS="2", CUDA_VISIBLE_DEVICES="")
+
+    def log(phase):
+        return {"output_dir": str(tmp_path / "ck" / phase), "log_dir": str(tmp_path / "logs" / phase), "log_every_steps": 1,
+                "save_every_steps": 2, "eval_every_steps": 1, "keep_last_n": 2, "use_wandb": False}
+
+    def run(module, cfg, done):
+        path = tmp_path / f"{module.rsplit('.', 1)[-1]}.yaml"
+        path.write_text(yaml.safe_dump(cfg))
+        cmd = [sys.executable, "-m", "dla_b200.cli.launch", "--cpu", "--nproc", "2", "--port", str(_free_port()), "-m", module,
+               "--config", str(path)]
+        res = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=400)
+        assert res.returncode == 0, f"{module}:\n" + res.stdout[-2500:] + res.stderr[-2500:]
+        assert done in res.stdout, res.stdout[-1500:]
+
+    hw = {"device": "cpu", "sharding": "zero3"}
+    run("dla_b200.cli.train_sft", {
+        "seed": 1, "model": {"model_name_or_path": "tiny-llama", "max_seq_length": 48},
+        "data": {"source": "local", "train_path": str(tmp_path / "sft.jsonl"), "eval_path": str(tmp_path / "sft.jsonl"), "num_workers": 0},
+        "optimization": {"micro_batch_size": 2, "learning_rate": 1e-3, "warmup_steps": 1, "max_train_steps": 3},
+        "logging": log("sft"), "hardware": {**hw, "gradient_accumulation_steps": 2}}, "Training complete")
+    latest = tmp_path / "ck" / "sft" / "latest"
+    assert (latest / "model.safetensors").exists()
+    run("dla_b200.cli.train_reward", {
+        "seed": 2, "model": {"base_model_name_or_path": str(latest), "pooling": "mean", "dropout": 0.1, "max_seq_length": 48},
+        "data": {"source": "local", "train_path": str(tmp_path / "pref.jsonl"), "eval_path": str(tmp_path / "pref.jsonl"), "num_workers": 0},
+        "optimization": {"micro_batch_size": 2, "learning_rate": 1e-3, "max_train_steps": 2},
+        "logging": log("reward"), "hardware": hw}, "Reward model training complete")
+    assert (tmp_path / "ck" / "reward" / "latest" / "pytorch_model.bin").exists()
+    run("dla_b200.cli.train_distill", {
+        "seed": 4, "model": {"student_model_name_or_path": "tiny-llama", "max_seq_length": 48},
+        "data": {"teacher_samples_path": str(tmp_path / "roll.jsonl"), "num_workers": 0},
+        "optimization": {"micro_batch_size": 2, "learning_rate": 1e-3, "max_train_steps": 2, "temperature": 2.0},
+        "distill": {"use_kl": True, "on_policy": True, "teacher_model_names_or_paths": [str(latest), "tiny-llama"]},
+        "logging": log("distill"), "hardware": hw}, "Distillation complete")
+    m = [json.loads(l) for l in (tmp_path / "logs" / "sft" / "metrics.jsonl").read_text().splitlines()]
+    assert any("eval/loss" in x for x in m) and any("train/loss" in x for x in m)
